@@ -1,0 +1,122 @@
+/*
+ * tomo_tv_b200 -- C ABI of the B200-native tomo_TV iterative-reconstruction engine.
+ *
+ * This is the drop-in boundary for the reference's GPU path: one function per method the
+ * reference binds on its pybind11 class `tomoengine`
+ * (/root/reference/tomofusion/gpu/utils/tomoengine.cpp:487-534), with the same names, argument
+ * meaning and host-side data layouts, so the reference's Python layer (TomoGPU,
+ * tomofusion/gpu/reconstructor.py:12-215; pytvlib.initialize_algorithm/run, tomofusion/pytvlib.py:5-31)
+ * can sit on top unchanged.  Plain pointers and sizes only; no torch / pybind / ASTRA types.
+ *
+ * Conventions
+ *   - every function returns 0 on success, non-zero on error; ttv_last_error() gives the message
+ *     (the reference aborts the process through ASTRA_ASSERT or ignores CUDA errors).
+ *   - host arrays are float32, C-contiguous, in the reference's layouts:
+ *       volume slice  [Ny][Nz]            (Matrix3D::getData/setData, container/Matrix3D.cpp:25-42)
+ *       tilt series   [Nslice][Nproj*Nray], b[s][a*Nray + d]   (reconstructor.py:54-56, tomoengine.cpp:101)
+ *   - inputs are copied; getters fill caller-provided buffers (ownership as in the reference).
+ *   - calls are synchronous with respect to the host, like the reference's bound methods.
+ *   - there is no CPU fallback: every entry point fails if no CUDA device is usable.
+ */
+#ifndef TOMO_TV_B200_H
+#define TOMO_TV_B200_H
+#include <stddef.h>
+#include <stdint.h>
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+typedef struct ttv_engine* ttv_handle;
+
+const char* ttv_last_error(void);
+int ttv_version(void);
+int ttv_device_count(int* count);                 /* replaces tomofusion.device_count, tomofusion/__init__.py:10-18 */
+
+/* tomoengine(Nslice, Nray) / tomoengine(Nslice, Nray, angles[rad])   tomoengine.cpp:34-84, :491-492.
+ * device < 0: current device.  angles may be NULL with nangles == 0. */
+int ttv_create(ttv_handle* out, int nslice, int nray, const float* angles_rad, int nangles, int device);
+/* Slab constructor for tilt-axis sharding (replaces multigpuengine's OpenMP slice fan-out,
+ * multigpuengine.cpp:113-228): this engine owns global slices [x_offset, x_offset+nslice_local). */
+int ttv_create_slab(ttv_handle* out, int nslice_local, int nray, const float* angles_rad, int nangles,
+                    int device, int x_offset, int nslice_global);
+int ttv_destroy(ttv_handle h);
+
+/* --- data in / out ------------------------------------------------------------------------ */
+int ttv_set_tilt_series(ttv_handle h, const float* b, int rows, int cols);          /* tomoengine.cpp:101 */
+int ttv_get_projections(ttv_handle h, float* out);                                  /* :456 */
+int ttv_get_model_projections(ttv_handle h, float* out);                            /* :459 */
+int ttv_initialize_initial_volume(ttv_handle h);                                    /* :95  */
+int ttv_initialize_recon_copy(ttv_handle h);                                        /* :98  */
+int ttv_set_original_volume(ttv_handle h, const float* slice, int s);               /* :104 */
+int ttv_set_recon(ttv_handle h, const float* slice, int s);                         /* :106 */
+int ttv_get_recon(ttv_handle h, float* out, int s);                                 /* :453 */
+int ttv_update_projection_angles(ttv_handle h, const float* angles_rad, int nangles); /* :130-149 */
+int ttv_create_projections(ttv_handle h);                                           /* :109-127 */
+int ttv_restart_recon(ttv_handle h);                                                /* :462-468 */
+int ttv_get_gpu_id(ttv_handle h, int* id);                                          /* :92 */
+int ttv_set_gpu(ttv_handle h, int id);                                              /* :87-89 */
+int ttv_poisson_noise(ttv_handle h, int Nc);                                        /* :471-484 */
+/* bulk variants (additions): whole volume [Nslice][Ny][Nz] in one call */
+int ttv_get_recon_all(ttv_handle h, float* out);
+int ttv_set_recon_all(ttv_handle h, const float* in);
+int ttv_set_original_volume_all(ttv_handle h, const float* in);
+
+/* --- algorithms --------------------------------------------------------------------------- */
+int ttv_initialize_SART(ttv_handle h, const char* order);                           /* :151-159 */
+int ttv_SART(ttv_handle h, float beta, int niter);                                  /* :162-179 */
+int ttv_initialize_SIRT(ttv_handle h);                                              /* :181-186 */
+int ttv_SIRT(ttv_handle h, int niter);                                              /* :189-205 */
+int ttv_initialize_FP(ttv_handle h);                                                /* :249-254 */
+int ttv_initialize_BP(ttv_handle h);                                                /* :271-276 */
+int ttv_initialize_poisson_ML(ttv_handle h);                                        /* :231-246 */
+int ttv_poisson_ML(ttv_handle h, float lambda, float* cost);                        /* :293-315 */
+int ttv_forward_projection(ttv_handle h);                                           /* :416-427 */
+int ttv_initialize_fista(ttv_handle h);                                             /* :350-372 */
+int ttv_get_lipschitz(ttv_handle h, float* L);                                      /* :375 */
+int ttv_fista_momentum(ttv_handle h, float beta);                                   /* :381-384 */
+int ttv_remove_momentum(ttv_handle h);                                              /* :378 */
+int ttv_initialize_CGLS(ttv_handle h);                                              /* :207-211 */
+int ttv_CGLS(ttv_handle h, int niter);                                              /* :214-229 */
+int ttv_initialize_FBP(ttv_handle h, const char* filter);                           /* :317-327 */
+int ttv_FBP(ttv_handle h, int apply_positivity);                                    /* :330-347 */
+
+/* --- regularisers, elementwise, reductions ---------------------------------------------------- */
+int ttv_tv_fgp(ttv_handle h, int ng, float lambda, float* tv_of_input);             /* :450 -> regularizers/tv_fgp.cu:192-281 */
+int ttv_tv_gd(ttv_handle h, int ng, float dPOCS, float* tv_of_input);               /* :447 -> regularizers/tv_gd.cu:141-218 */
+int ttv_tv(ttv_handle h, float* tv);                                                /* :441 */
+int ttv_original_tv(ttv_handle h, float* tv);                                       /* :444 */
+int ttv_soft_threshold(ttv_handle h, float lambda);                                 /* :436-438 */
+int ttv_l1_norm(ttv_handle h, float* v);                                            /* :433 */
+int ttv_copy_recon(ttv_handle h);                                                   /* :404 */
+int ttv_matrix_2norm(ttv_handle h, float* v);                                       /* :407 */
+int ttv_data_distance(ttv_handle h, float* v);                                      /* :410-413 */
+int ttv_rmse(ttv_handle h, float* v);                                               /* :430 */
+
+/* --- multi-GPU plumbing (one process per GPU; NCCL halo exchange + scalar all-reduce) --------
+ * Replaces the unbuilt MPI variant's MPI_Isend/Recv + MPI_Allreduce
+ * (tomofusion/gpu/utils/mpi_astra_ctvlib.cpp:360-386,160). */
+int ttv_nccl_unique_id(void* id128);                       /* rank 0: 128-byte ncclUniqueId to broadcast */
+int ttv_comm_init(ttv_handle h, const void* id128, int rank, int nranks);
+
+/* --- measurement / test hooks (not part of the reference API) ------------------------------- */
+int ttv_sync(ttv_handle h);
+/* device-side __cosf/__sinf of the per-angle FP angle, as the projector evaluates them */
+int ttv_get_trig(ttv_handle h, float* cosv, float* sinv);
+/* R = inv(FP(1)) [Nproj*Nray], C = inv(BP(1)) [Ny*Nz]   (A/cuda/2d/sirt.cu:112-147) */
+int ttv_get_sirt_weights(ttv_handle h, float* R, float* C);
+/* back-project the model projections g into recon (vol = BP(g)); operator-level parity tests */
+int ttv_back_projection(ttv_handle h);
+int ttv_set_model_projections(ttv_handle h, const float* g, int rows, int cols);
+/* time `reps` back-to-back launches of one named kernel group with CUDA events on the engine's
+ * stream; *ms = average per launch.  names: fp, bp, sirt, fgp_sweep, fgp_first, fgp_final, fgp,
+ * tv, momentum, tvgd_grad, tvgd_update, sqdist, fista_iter, kl, sart. */
+int ttv_time_kernel(ttv_handle h, const char* name, int reps, int arg_i, float arg_f, float* ms);
+/* number of kernel launches issued by this engine so far */
+int ttv_launch_count(ttv_handle h, long long* n);
+/* algorithmic geometry facts for the roofline: bytes of one volume (V) and one sinogram (S) */
+int ttv_sizes(ttv_handle h, long long* V, long long* S, long long* samples_per_projection);
+
+#ifdef __cplusplus
+}
+#endif
+#endif

@@ -1,0 +1,274 @@
+"""ctypes front-end of oracle/liboracle.so (oracle.c) -- TEST INFRASTRUCTURE ONLY.
+
+`Oracle` mirrors the observable semantics of the reference's `tomoengine` class
+(/root/reference/tomofusion/gpu/utils/tomoengine.cpp) on the CPU so parity tests can run the same
+call sequence against both.  It is never imported by the product package.
+"""
+import ctypes as C
+import os
+import subprocess
+import numpy as np
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+_LIB = None
+
+f32p = np.ctypeslib.ndpointer(dtype=np.float32, flags="C_CONTIGUOUS")
+i32p = np.ctypeslib.ndpointer(dtype=np.int32, flags="C_CONTIGUOUS")
+
+
+class AngleConst(C.Structure):
+    _fields_ = [("angle", C.c_float), ("detsize", C.c_float), ("offset", C.c_float),
+                ("sc", C.c_float), ("ss", C.c_float), ("off", C.c_float), ("scale", C.c_float),
+                ("rayX", C.c_float), ("rayY", C.c_float), ("vertical", C.c_int32)]
+
+
+def build():
+    """Compile oracle.c -> liboracle.so (gcc, seconds)."""
+    subprocess.check_call(["make", "-s", "-C", _HERE, "liboracle.so"])
+
+
+def lib():
+    global _LIB
+    if _LIB is None:
+        path = os.path.join(_HERE, "liboracle.so")
+        if not os.path.exists(path) or os.path.getmtime(path) < os.path.getmtime(os.path.join(_HERE, "oracle.c")):
+            build()
+        _LIB = C.CDLL(path)
+        L = _LIB
+        vp = C.c_void_p
+        L.orc_geometry.argtypes = [C.c_int, C.c_int, f32p, vp]
+        L.orc_fp.argtypes = [f32p, f32p, C.c_int, C.c_int, C.c_int, C.c_int, vp, vp, vp, C.c_float, C.c_int]
+        L.orc_bp.argtypes = [f32p, f32p, C.c_int, C.c_int, C.c_int, C.c_int, vp, C.c_float, C.c_int]
+        L.orc_bp_sart.argtypes = [f32p, f32p, C.c_int, C.c_int, C.c_int, vp, C.c_float, C.c_int]
+        L.orc_sirt_weights.argtypes = [f32p, f32p, C.c_int, C.c_int, C.c_int, C.c_int, vp, vp, vp, C.c_int]
+        L.orc_fp3d.argtypes = [f32p, f32p, C.c_int, C.c_int, C.c_int, vp, vp, vp, C.c_int]
+        L.orc_bp3d.argtypes = [f32p, f32p, C.c_int, C.c_int, C.c_int, vp, C.c_int]
+        L.orc_sirt3d.argtypes = [f32p, f32p, f32p, f32p, C.c_int, C.c_int, C.c_int, vp, vp, vp, C.c_int, C.c_int]
+        L.orc_sart3d.argtypes = [f32p, f32p, f32p, C.c_int, C.c_int, C.c_int, vp, vp, vp, vp, C.c_int, C.c_float, C.c_int]
+        L.orc_lipschitz.argtypes = [C.c_int, C.c_int, vp, vp, vp, C.c_int]
+        L.orc_lipschitz.restype = C.c_float
+        L.orc_kl3d.argtypes = [f32p, f32p, C.c_int, C.c_int, C.c_int, vp, vp, vp, C.c_float, C.c_float, C.c_int]
+        L.orc_kl3d.restype = C.c_float
+        L.orc_tv.argtypes = [f32p, C.c_int, C.c_int, C.c_int]
+        L.orc_tv.restype = C.c_double
+        L.orc_tv_gradient.argtypes = [f32p, f32p, C.c_int, C.c_int, C.c_int]
+        L.orc_tv_gd.argtypes = [f32p, C.c_int, C.c_float, C.c_int, C.c_int, C.c_int]
+        L.orc_tv_gd.restype = C.c_float
+        L.orc_tv_fgp.argtypes = [f32p, C.c_int, C.c_float, C.c_int, C.c_int, C.c_int]
+        L.orc_tv_fgp.restype = C.c_float
+        L.orc_momentum.argtypes = [f32p, f32p, f32p, C.c_float, C.c_size_t]
+        L.orc_soft_threshold.argtypes = [f32p, C.c_float, C.c_size_t]
+        L.orc_positivity.argtypes = [f32p, C.c_size_t]
+        for nm in ("orc_sqdist",):
+            getattr(L, nm).argtypes = [f32p, f32p, C.c_size_t]
+            getattr(L, nm).restype = C.c_double
+        for nm in ("orc_sum", "orc_l1", "orc_sumsq"):
+            getattr(L, nm).argtypes = [f32p, C.c_size_t]
+            getattr(L, nm).restype = C.c_double
+        L.orc_num_threads.restype = C.c_int
+    return _LIB
+
+
+def _ptr(a):
+    return None if a is None else a.ctypes.data_as(C.c_void_p)
+
+
+class Geometry:
+    """Per-angle constants (orc_geometry).  cosv/sinv optionally override cosf/sinf with the
+    device-evaluated __cosf/__sinf tables so kernel-vs-oracle comparisons are not dominated by the
+    fast-intrinsic error."""
+
+    def __init__(self, angles_rad, ndet, cosv=None, sinv=None):
+        self.angles = np.ascontiguousarray(angles_rad, dtype=np.float32)
+        self.na = int(self.angles.size)
+        self.nd = int(ndet)
+        self.buf = (AngleConst * self.na)()
+        lib().orc_geometry(self.na, self.nd, self.angles, C.cast(self.buf, C.c_void_p))
+        self.cosv = None if cosv is None else np.ascontiguousarray(cosv, dtype=np.float32)
+        self.sinv = None if sinv is None else np.ascontiguousarray(sinv, dtype=np.float32)
+
+    @property
+    def p(self):
+        return C.cast(self.buf, C.c_void_p)
+
+    def table(self):
+        """(na, 10) float64 view of the constants for inspection."""
+        return np.array([[getattr(g, f) for f, _ in AngleConst._fields_] for g in self.buf], dtype=np.float64)
+
+
+def fp2d(vol, geo, outscale=1.0, quant=1, sino=None):
+    H, W = vol.shape
+    if sino is None:
+        sino = np.zeros((geo.na, geo.nd), np.float32)
+    lib().orc_fp(np.ascontiguousarray(vol, np.float32), sino, W, H, geo.na, geo.nd, geo.p,
+                 _ptr(geo.cosv), _ptr(geo.sinv), outscale, quant)
+    return sino
+
+
+def bp2d(sino, geo, shape, outscale=1.0, quant=1, vol=None):
+    H, W = shape
+    if vol is None:
+        vol = np.zeros((H, W), np.float32)
+    lib().orc_bp(vol, np.ascontiguousarray(sino, np.float32), W, H, geo.na, geo.nd, geo.p, outscale, quant)
+    return vol
+
+
+class Oracle:
+    """CPU mirror of tomoengine's state machine (tomoengine.cpp:48-484), float32, [x][y][z]."""
+
+    def __init__(self, nslice, nray, angles_rad, quant=1, cosv=None, sinv=None):
+        self.nx, self.n = int(nslice), int(nray)
+        self.quant = int(quant)
+        self.geo = Geometry(angles_rad, nray, cosv, sinv)
+        self.na = self.geo.na
+        self.recon = np.zeros((self.nx, self.n, self.n), np.float32)
+        self.b = np.zeros((self.nx, self.na * self.n), np.float32)
+        self.g = np.zeros_like(self.b)
+        self.momentum = False
+        self.yk = self.recon_old = self.temp = self.original = None
+        self.R = self.C = None
+        self.order = None
+        self.relax = 1.0
+        self.L_A = self.L_Aml = None
+
+    # -- data ------------------------------------------------------------------------------
+    def set_tilt_series(self, b):
+        self.b = np.ascontiguousarray(b, dtype=np.float32).reshape(self.nx, self.na * self.n).copy()
+
+    def set_original_volume(self, m, s):
+        if self.original is None:
+            self.original = np.zeros_like(self.recon)
+        self.original[s] = m
+
+    def initialize_initial_volume(self):
+        self.original = np.zeros_like(self.recon)
+
+    def initialize_recon_copy(self):
+        self.temp = np.zeros_like(self.recon)
+
+    def get_recon(self, s):
+        return self.recon[s].copy()
+
+    def set_recon(self, m, s):
+        self.recon[s] = m
+
+    def restart_recon(self):
+        self.recon[:] = 0
+        if self.momentum:
+            self.yk[:] = 0
+            self.recon_old[:] = 0
+
+    # -- operators -------------------------------------------------------------------------
+    def _weights(self):
+        if self.R is None:
+            self.R = np.zeros((self.na, self.n), np.float32)
+            self.C = np.zeros((self.n, self.n), np.float32)
+            lib().orc_sirt_weights(self.R, self.C, self.n, self.n, self.na, self.n, self.geo.p,
+                                   _ptr(self.geo.cosv), _ptr(self.geo.sinv), self.quant)
+
+    def initialize_SIRT(self):
+        self._weights()
+
+    def initialize_SART(self, order="sequential"):
+        self._weights()
+        self.order = np.arange(self.na, dtype=np.int32)
+        self.sart_order_name = order
+
+    def initialize_FP(self):
+        pass
+
+    def initialize_BP(self):
+        pass
+
+    def lipschitz(self):
+        return lib().orc_lipschitz(self.n, self.na, self.geo.p, _ptr(self.geo.cosv), _ptr(self.geo.sinv), self.quant)
+
+    def initialize_fista(self):
+        self.momentum = True
+        self.yk = self.recon.copy()
+        self.recon_old = self.recon.copy()
+        self._weights()
+        self.L_A = self.lipschitz()
+
+    def get_lipschitz(self):
+        return self.L_A
+
+    def remove_momentum(self):
+        self.momentum = False
+
+    def initialize_poisson_ML(self):
+        self.L_Aml = self.lipschitz()
+        m = self.b.max()
+        if m > 1:
+            self.b = (self.b / m).astype(np.float32)
+
+    def SIRT(self, niter):
+        tgt = self.yk if self.momentum else self.recon
+        lib().orc_sirt3d(tgt, self.b, self.R, self.C, self.nx, self.n, self.na, self.geo.p,
+                         _ptr(self.geo.cosv), _ptr(self.geo.sinv), niter, self.quant)
+
+    def SART(self, beta, niter):
+        if beta != 1:
+            self.relax = float(beta)      # sticky, tomoengine.cpp:172
+        lib().orc_sart3d(self.recon, self.b, self.R, self.nx, self.n, self.na, self.geo.p,
+                         _ptr(self.geo.cosv), _ptr(self.geo.sinv), _ptr(self.order), niter, self.relax, self.quant)
+
+    def poisson_ML(self, lam):
+        return lib().orc_kl3d(self.recon, self.b, self.nx, self.n, self.na, self.geo.p,
+                              _ptr(self.geo.cosv), _ptr(self.geo.sinv), lam, self.L_Aml, self.quant)
+
+    def forward_projection(self):
+        lib().orc_fp3d(self.recon, self.g, self.nx, self.n, self.na, self.geo.p,
+                       _ptr(self.geo.cosv), _ptr(self.geo.sinv), self.quant)
+
+    def create_projections(self):
+        lib().orc_fp3d(self.original, self.b, self.nx, self.n, self.na, self.geo.p,
+                       _ptr(self.geo.cosv), _ptr(self.geo.sinv), self.quant)
+
+    def back_projection_of(self, sino):
+        out = np.zeros_like(self.recon)
+        lib().orc_bp3d(out, np.ascontiguousarray(sino, np.float32), self.nx, self.n, self.na, self.geo.p, self.quant)
+        return out
+
+    def data_distance(self):
+        self.forward_projection()
+        return float(np.sqrt(lib().orc_sqdist(self.g, self.b, self.g.size)))
+
+    def get_projections(self):
+        return self.b.copy()
+
+    def get_model_projections(self):
+        return self.g.copy()
+
+    # -- regularisers / elementwise -----------------------------------------------------------
+    def tv(self):
+        return float(lib().orc_tv(self.recon, self.nx, self.n, self.n))
+
+    def original_tv(self):
+        return float(lib().orc_tv(self.original, self.nx, self.n, self.n))
+
+    def tv_gd(self, ng, dPOCS):
+        return lib().orc_tv_gd(self.recon, ng, dPOCS, self.nx, self.n, self.n)
+
+    def tv_fgp(self, ng, lam):
+        return lib().orc_tv_fgp(self.recon, ng, lam, self.nx, self.n, self.n)
+
+    def fista_momentum(self, beta):
+        lib().orc_momentum(self.recon, self.yk, self.recon_old, beta, self.recon.size)
+
+    def copy_recon(self):
+        self.temp[:] = self.recon
+
+    def matrix_2norm(self):
+        return float(np.sqrt(lib().orc_sqdist(self.recon, self.temp, self.recon.size)))
+
+    def rmse(self):
+        return float(np.sqrt(lib().orc_sqdist(self.recon, self.original, self.recon.size) / self.recon.size))
+
+    def l1_norm(self):
+        return float(lib().orc_l1(self.recon, self.recon.size))
+
+    def soft_threshold(self, lam):
+        tgt = self.yk if self.momentum else self.recon
+        lib().orc_soft_threshold(tgt.reshape(-1), lam, tgt.size)
+        lib().orc_positivity(tgt.reshape(-1), tgt.size)

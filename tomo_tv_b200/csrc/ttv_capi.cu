@@ -1,0 +1,356 @@
+// C ABI of the engine (include/tomo_tv_b200.h).  Every entry point mirrors one bound method of the
+// reference's pybind11 class (T/gpu/utils/tomoengine.cpp:487-534); errors become status codes +
+// ttv_last_error() instead of the reference's process abort.
+#include "../../include/tomo_tv_b200.h"
+#include "ttv_engine.cuh"
+#include "ttv_sart.cuh"
+#include "ttv_fbp.cuh"
+
+using namespace ttv;
+
+struct ttv_engine { Engine* e; };
+
+static thread_local std::string g_err;
+
+#define TTV_TRY try {
+#define TTV_CATCH                                                      \
+    return 0; }                                                        \
+    catch (const std::exception& ex) { g_err = ex.what(); return 1; } \
+    catch (...) { g_err = "unknown error"; return 2; }
+
+static Engine& E(ttv_handle h) {
+    if (!h || !h->e) throw CudaError("null engine handle");
+    h->e->use();
+    return *h->e;
+}
+
+extern "C" {
+
+const char* ttv_last_error(void) { return g_err.c_str(); }
+int ttv_version(void) { return 100; }
+
+int ttv_device_count(int* count) {
+    TTV_TRY
+    int c = 0;
+    cudaError_t e = cudaGetDeviceCount(&c);
+    if (e != cudaSuccess) { cudaGetLastError(); c = 0; }
+    *count = c;
+    TTV_CATCH
+}
+
+int ttv_create(ttv_handle* out, int nslice, int nray, const float* angles, int nangles, int device) {
+    return ttv_create_slab(out, nslice, nray, angles, nangles, device, 0, nslice);
+}
+int ttv_create_slab(ttv_handle* out, int nslice_local, int nray, const float* angles, int nangles, int device, int x_offset, int nslice_global) {
+    TTV_TRY
+    *out = nullptr;
+    ttv_engine* h = new ttv_engine{nullptr};
+    try { h->e = new Engine(nslice_local, nray, angles, nangles, device, x_offset, nslice_global); }
+    catch (...) { delete h; throw; }
+    *out = h;
+    TTV_CATCH
+}
+int ttv_destroy(ttv_handle h) {
+    TTV_TRY
+    if (h) { delete h->e; delete h; }
+    TTV_CATCH
+}
+
+// ------------------------------------------------------------------ data
+int ttv_set_tilt_series(ttv_handle h, const float* b, int rows, int cols) {
+    TTV_TRY
+    Engine& e = E(h); e.need_angles();
+    if (rows != e.nx || cols != e.Na * e.N) throw CudaError("set_tilt_series: expected a [Nslice, Nproj*Nray] matrix");
+    e.upload(e.b, b, (int64_t)e.Na * e.N);
+    TTV_CATCH
+}
+int ttv_set_model_projections(ttv_handle h, const float* g, int rows, int cols) {
+    TTV_TRY
+    Engine& e = E(h); e.need_angles();
+    if (rows != e.nx || cols != e.Na * e.N) throw CudaError("set_model_projections: expected a [Nslice, Nproj*Nray] matrix");
+    e.upload(e.g, g, (int64_t)e.Na * e.N);
+    TTV_CATCH
+}
+int ttv_get_projections(ttv_handle h, float* out) { TTV_TRY Engine& e = E(h); e.need_angles(); e.download(e.b, out, (int64_t)e.Na * e.N); TTV_CATCH }
+int ttv_get_model_projections(ttv_handle h, float* out) { TTV_TRY Engine& e = E(h); e.need_angles(); e.download(e.g, out, (int64_t)e.Na * e.N); TTV_CATCH }
+int ttv_initialize_initial_volume(ttv_handle h) { TTV_TRY Engine& e = E(h); e.original.alloc(e.vol_elems()); TTV_CATCH }
+int ttv_initialize_recon_copy(ttv_handle h) { TTV_TRY Engine& e = E(h); e.temp.alloc(e.vol_elems()); TTV_CATCH }
+int ttv_set_original_volume(ttv_handle h, const float* s, int i) { TTV_TRY Engine& e = E(h); if (!e.original.ok()) e.original.alloc(e.vol_elems()); e.set_slice(e.original, s, i); TTV_CATCH }
+int ttv_set_recon(ttv_handle h, const float* s, int i) { TTV_TRY Engine& e = E(h); e.set_slice(e.recon, s, i); TTV_CATCH }
+int ttv_get_recon(ttv_handle h, float* out, int i) { TTV_TRY Engine& e = E(h); e.get_slice(e.recon, out, i); TTV_CATCH }
+int ttv_get_recon_all(ttv_handle h, float* out) { TTV_TRY Engine& e = E(h); e.download(e.recon, out, (int64_t)e.N * e.N); TTV_CATCH }
+int ttv_set_recon_all(ttv_handle h, const float* in) { TTV_TRY Engine& e = E(h); e.upload(e.recon, in, (int64_t)e.N * e.N); TTV_CATCH }
+int ttv_set_original_volume_all(ttv_handle h, const float* in) {
+    TTV_TRY Engine& e = E(h); if (!e.original.ok()) e.original.alloc(e.vol_elems()); e.upload(e.original, in, (int64_t)e.N * e.N); TTV_CATCH
+}
+int ttv_update_projection_angles(ttv_handle h, const float* a, int n) { TTV_TRY Engine& e = E(h); e.set_angles(a, n); TTV_CATCH }
+int ttv_create_projections(ttv_handle h) {
+    TTV_TRY
+    Engine& e = E(h);
+    if (!e.original.ok()) throw CudaError("create_projections: original volume not set");
+    e.fp<FP_STORE>(e.original.p, e.b.p, nullptr, nullptr);
+    e.sync();
+    TTV_CATCH
+}
+int ttv_restart_recon(ttv_handle h) {
+    TTV_TRY
+    Engine& e = E(h);
+    TTV_CUDA(cudaMemsetAsync(e.recon.p, 0, e.vol_elems() * sizeof(float), e.st));
+    if (e.momentum) {
+        TTV_CUDA(cudaMemsetAsync(e.yk.p, 0, e.vol_elems() * sizeof(float), e.st));
+        TTV_CUDA(cudaMemsetAsync(e.recon_old.p, 0, e.vol_elems() * sizeof(float), e.st));
+    }
+    e.sync();
+    TTV_CATCH
+}
+int ttv_get_gpu_id(ttv_handle h, int* id) { TTV_TRY *id = E(h).gpuID; TTV_CATCH }
+int ttv_set_gpu(ttv_handle h, int id) { TTV_TRY E(h).gpuID = id; TTV_CATCH }   /* only records the index (tomoengine.cpp:87-89) */
+
+// b <- Poisson(b / sum(b) * Nc * size) / (Nc*size) * sum(b)     (tomoengine.cpp:471-484); host-side simulation helper
+int ttv_poisson_noise(ttv_handle h, int Nc) {
+    TTV_TRY
+    Engine& e = E(h); e.need_angles();
+    const size_t M = (size_t)e.Na * e.N, n = (size_t)e.nx * M;
+    std::vector<float> hb(n);
+    e.download(e.b, hb.data(), (int64_t)M);
+    double sum = 0; for (float v : hb) sum += v;
+    sum = e.allreduce_sum(sum);
+    const double tot = (double)Nc * (double)((size_t)e.nxg * M);
+    std::default_random_engine gen((unsigned)(1 + e.rank));
+    for (size_t i = 0; i < n; ++i) {
+        const double mean = hb[i] / sum * tot;
+        std::poisson_distribution<int> dist(mean > 0 ? mean : 0.0);
+        hb[i] = (float)(dist(gen) / tot * sum);
+    }
+    e.upload(e.b, hb.data(), (int64_t)M);
+    TTV_CATCH
+}
+
+// ------------------------------------------------------------------ algorithms
+int ttv_initialize_SIRT(ttv_handle h) { TTV_TRY E(h).compute_weights(); TTV_CATCH }
+int ttv_SIRT(ttv_handle h, int niter) {
+    TTV_TRY
+    Engine& e = E(h);
+    if (!e.weights_ready) throw CudaError("SIRT called before initialize_SIRT");
+    float* tgt = e.momentum ? e.yk.p : e.recon.p;           // tomoengine.cpp:194-195
+    for (int i = 0; i < niter; ++i) e.sirt_step(tgt);
+    e.sync();
+    TTV_CATCH
+}
+int ttv_initialize_SART(ttv_handle h, const char* order) {
+    TTV_TRY
+    Engine& e = E(h);
+    e.projOrder = order ? order : "sequential";
+    e.compute_weights();
+    e.sart_ready = true;
+    TTV_CATCH
+}
+int ttv_SART(ttv_handle h, float beta, int niter) { TTV_TRY E(h).sart_pass(beta, niter); TTV_CATCH }
+int ttv_initialize_FP(ttv_handle h) { TTV_TRY E(h).need_angles(); E(h).fp_ready = true; TTV_CATCH }
+int ttv_initialize_BP(ttv_handle h) { TTV_TRY E(h).need_angles(); TTV_CATCH }
+
+int ttv_initialize_poisson_ML(ttv_handle h) {
+    TTV_TRY
+    Engine& e = E(h);
+    e.compute_weights();
+    e.L_Aml = e.L_A;                                         // max(BP(FP(1))), tomoengine.cpp:241-242
+    const float m = e.max_of(e.b.p, e.sino_elems());        // b /= max(b) if max(b) > 1, :245
+    if (m > 1.0f) {
+        div_kernel<<<ew_blocks(e.sino_elems() / 4), 256, 0, e.st>>>(reinterpret_cast<float4*>(e.b.p), m, e.sino_elems() / 4);
+        ++e.launches;
+    }
+    e.kl_ready = true;
+    e.sync();
+    TTV_CATCH
+}
+int ttv_poisson_ML(ttv_handle h, float lambda, float* cost) {
+    TTV_TRY
+    Engine& e = E(h);
+    if (!e.kl_ready) throw CudaError("poisson_ML called before initialize_poisson_ML");
+    if (!e.r.ok()) e.r.alloc(e.sino_elems());
+    e.zero_red(3);
+    e.fp<FP_KL>(e.recon.p, e.r.p, e.b.p, e.d_red + 3, -1, 1e-1f);
+    e.bp<BP_STEP_UPD>(e.r.p, e.recon.p, lambda / e.L_Aml);
+    *cost = (float)e.read_red(3);
+    TTV_CATCH
+}
+int ttv_forward_projection(ttv_handle h) { TTV_TRY Engine& e = E(h); e.fp<FP_STORE>(e.recon.p, e.g.p, nullptr, nullptr); e.sync(); TTV_CATCH }
+int ttv_back_projection(ttv_handle h) { TTV_TRY Engine& e = E(h); e.bp<BP_STORE>(e.g.p, e.recon.p); e.sync(); TTV_CATCH }
+
+int ttv_initialize_fista(ttv_handle h) {
+    TTV_TRY
+    Engine& e = E(h);
+    e.momentum = true;
+    e.yk.alloc(e.vol_elems()); e.recon_old.alloc(e.vol_elems());
+    TTV_CUDA(cudaMemcpyAsync(e.yk.p, e.recon.p, e.vol_elems() * sizeof(float), cudaMemcpyDeviceToDevice, e.st));
+    TTV_CUDA(cudaMemcpyAsync(e.recon_old.p, e.recon.p, e.vol_elems() * sizeof(float), cudaMemcpyDeviceToDevice, e.st));
+    e.compute_weights();                                     // initializeSIRT + L_A (tomoengine.cpp:364-371)
+    e.sync();
+    TTV_CATCH
+}
+int ttv_get_lipschitz(ttv_handle h, float* L) { TTV_TRY *L = E(h).L_A; TTV_CATCH }
+int ttv_remove_momentum(ttv_handle h) { TTV_TRY E(h).momentum = false; TTV_CATCH }
+int ttv_fista_momentum(ttv_handle h, float beta) {
+    TTV_TRY
+    Engine& e = E(h);
+    if (!e.yk.ok()) throw CudaError("fista_momentum called before initialize_fista");
+    const size_t n4 = e.vol_elems() / 4;
+    momentum_kernel<<<ew_blocks(n4), 256, 0, e.st>>>(reinterpret_cast<float4*>(e.recon.p), reinterpret_cast<float4*>(e.yk.p),
+                                                      reinterpret_cast<float4*>(e.recon_old.p), beta, n4);
+    ++e.launches; TTV_LAUNCH_CHECK();
+    e.sync();
+    TTV_CATCH
+}
+
+// ------------------------------------------------------------------ regularisers & reductions
+int ttv_tv_fgp(ttv_handle h, int ng, float lambda, float* tv) { TTV_TRY *tv = E(h).tv_fgp(ng, lambda); TTV_CATCH }
+int ttv_tv_gd(ttv_handle h, int ng, float dPOCS, float* tv) { TTV_TRY *tv = E(h).tv_gd(ng, dPOCS); TTV_CATCH }
+int ttv_tv(ttv_handle h, float* tv) { TTV_TRY Engine& e = E(h); *tv = (float)e.tv_value(e.recon.p); TTV_CATCH }
+int ttv_original_tv(ttv_handle h, float* tv) {
+    TTV_TRY Engine& e = E(h); if (!e.original.ok()) throw CudaError("original volume not set"); *tv = (float)e.tv_value(e.original.p); TTV_CATCH
+}
+int ttv_soft_threshold(ttv_handle h, float lambda) {
+    TTV_TRY
+    Engine& e = E(h);
+    float* tgt = e.momentum ? e.yk.p : e.recon.p;           // tomoengine.cpp:436-438 (threshold, then positivity)
+    ew_kernel<EW_SOFT_POS><<<ew_blocks(e.vol_elems() / 4), 256, 0, e.st>>>(reinterpret_cast<float4*>(tgt), lambda, e.vol_elems() / 4);
+    ++e.launches; TTV_LAUNCH_CHECK(); e.sync();
+    TTV_CATCH
+}
+int ttv_l1_norm(ttv_handle h, float* v) { TTV_TRY Engine& e = E(h); *v = (float)e.reduce<RED_L1>(e.recon.p, nullptr, e.vol_elems()); TTV_CATCH }
+int ttv_copy_recon(ttv_handle h) {
+    TTV_TRY
+    Engine& e = E(h);
+    if (!e.temp.ok()) throw CudaError("copy_recon called before initialize_recon_copy");
+    TTV_CUDA(cudaMemcpyAsync(e.temp.p, e.recon.p, e.vol_elems() * sizeof(float), cudaMemcpyDeviceToDevice, e.st));
+    e.sync();
+    TTV_CATCH
+}
+int ttv_matrix_2norm(ttv_handle h, float* v) {
+    TTV_TRY
+    Engine& e = E(h);
+    if (!e.temp.ok()) throw CudaError("matrix_2norm called before initialize_recon_copy");
+    *v = (float)std::sqrt(e.reduce<RED_SQDIST>(e.recon.p, e.temp.p, e.vol_elems()));
+    TTV_CATCH
+}
+int ttv_data_distance(ttv_handle h, float* v) {
+    TTV_TRY
+    Engine& e = E(h);
+    e.zero_red(4);
+    e.fp<FP_STORE_DIST>(e.recon.p, e.g.p, e.b.p, e.d_red + 4);      // g = FP(recon) and ||g-b||^2 in one pass
+    *v = (float)std::sqrt(e.read_red(4));
+    TTV_CATCH
+}
+int ttv_rmse(ttv_handle h, float* v) {
+    TTV_TRY
+    Engine& e = E(h);
+    if (!e.original.ok()) throw CudaError("rmse: original volume not set");
+    const double s = e.reduce<RED_SQDIST>(e.recon.p, e.original.p, e.vol_elems());
+    *v = (float)std::sqrt(s / ((double)e.nxg * e.N * e.N));
+    TTV_CATCH
+}
+
+// ------------------------------------------------------------------ CGLS / FBP (ttv_fbp.cuh)
+int ttv_initialize_CGLS(ttv_handle h) { TTV_TRY E(h).need_angles(); TTV_CATCH }
+int ttv_CGLS(ttv_handle h, int niter) { TTV_TRY cgls_run(E(h), niter); TTV_CATCH }
+int ttv_initialize_FBP(ttv_handle h, const char* filter) { TTV_TRY Engine& e = E(h); e.need_angles(); e.fbpFilter = filter ? filter : "ram-lak"; TTV_CATCH }
+int ttv_FBP(ttv_handle h, int apply_positivity) { TTV_TRY fbp_run(E(h), apply_positivity != 0); TTV_CATCH }
+
+// ------------------------------------------------------------------ multi-GPU
+int ttv_nccl_unique_id(void* id128) {
+    TTV_TRY
+    Nccl& n = Nccl::get();
+    Nccl::uid_t id;
+    n.check(n.GetUniqueId(&id), "ncclGetUniqueId");
+    std::memcpy(id128, &id, 128);
+    TTV_CATCH
+}
+int ttv_comm_init(ttv_handle h, const void* id128, int rank, int nranks) {
+    TTV_TRY
+    Engine& e = E(h);
+    Nccl& n = Nccl::get();
+    Nccl::uid_t id; std::memcpy(&id, id128, 128);
+    n.check(n.CommInitRank(&e.comm, nranks, id, rank), "ncclCommInitRank");
+    e.rank = rank; e.nranks = nranks;
+    TTV_CATCH
+}
+
+// ------------------------------------------------------------------ measurement / test hooks
+int ttv_sync(ttv_handle h) { TTV_TRY E(h).sync(); TTV_CATCH }
+int ttv_get_trig(ttv_handle h, float* cosv, float* sinv) {
+    TTV_TRY
+    Engine& e = E(h); e.need_angles();
+    float *dc, *ds;
+    TTV_CUDA(cudaMalloc(&dc, e.Na * sizeof(float))); TTV_CUDA(cudaMalloc(&ds, e.Na * sizeof(float)));
+    trig_kernel<<<(e.Na + 127) / 128, 128, 0, e.st>>>(e.d_theta, dc, ds, e.Na); ++e.launches;
+    TTV_CUDA(cudaMemcpyAsync(cosv, dc, e.Na * sizeof(float), cudaMemcpyDeviceToHost, e.st));
+    TTV_CUDA(cudaMemcpyAsync(sinv, ds, e.Na * sizeof(float), cudaMemcpyDeviceToHost, e.st));
+    e.sync(); cudaFree(dc); cudaFree(ds);
+    TTV_CATCH
+}
+int ttv_get_sirt_weights(ttv_handle h, float* R, float* C) {
+    TTV_TRY
+    Engine& e = E(h); e.compute_weights();
+    TTV_CUDA(cudaMemcpyAsync(R, e.R.p, (size_t)e.Na * e.N * sizeof(float), cudaMemcpyDeviceToHost, e.st));
+    TTV_CUDA(cudaMemcpyAsync(C, e.C.p, (size_t)e.N * e.N * sizeof(float), cudaMemcpyDeviceToHost, e.st));
+    e.sync();
+    TTV_CATCH
+}
+int ttv_launch_count(ttv_handle h, long long* n) { TTV_TRY *n = E(h).launches; TTV_CATCH }
+int ttv_sizes(ttv_handle h, long long* V, long long* S, long long* samples) {
+    TTV_TRY
+    Engine& e = E(h);
+    *V = (long long)e.nx * e.N * e.N * 4;
+    *S = (long long)e.nx * e.Na * e.N * 4;
+    *samples = (long long)e.nx * e.Na * e.N * e.N;
+    TTV_CATCH
+}
+
+int ttv_time_kernel(ttv_handle h, const char* name, int reps, int arg_i, float arg_f, float* ms) {
+    TTV_TRY
+    Engine& e = E(h);
+    const std::string nm = name ? name : "";
+    const size_t n = e.vol_elems();
+    if (!e.r.ok() && e.Na > 0) e.r.alloc(e.sino_elems());
+    if (!e.scratch.ok()) e.scratch.alloc(n);
+    for (int i = 0; i < 6; ++i) if (!e.P[i].ok()) e.P[i].alloc(n);
+    if (!e.yk.ok()) e.yk.alloc(n);
+    if (!e.recon_old.ok()) e.recon_old.alloc(n);
+    if (e.Na > 0) e.compute_weights();
+    FgpParams fp; fp.in = e.recon.p; fp.P1 = e.P[0].p; fp.P2 = e.P[1].p; fp.P3 = e.P[2].p; fp.Q1 = e.P[3].p; fp.Q2 = e.P[4].p; fp.Q3 = e.P[5].p;
+    fp.hl_P1 = fp.hr_in = fp.hr_P1 = fp.hr_P2 = fp.hr_P3 = nullptr; fp.lambda = 0.1f; fp.multip = 1.0f / 2.6f; fp.d = e.dims();
+    dim3 gsw((e.N + TV_KSEG - 1) / TV_KSEG, (e.N + TV_WARPS - 1) / TV_WARPS, e.nxb);
+    GdParams gp; gp.x = e.recon.p; gp.g = e.scratch.p; gp.hm = gp.hp = nullptr; gp.sumsq = e.d_red + 1; gp.d = e.dims();
+    const int64_t rows = (int64_t)e.nxb * e.N;
+    auto one = [&]() {
+        if (nm == "fp") e.fp<FP_STORE>(e.recon.p, e.g.p, nullptr, nullptr);
+        else if (nm == "fp_sirt") e.fp<FP_SIRT_RES>(e.recon.p, e.r.p, e.b.p, nullptr);
+        else if (nm == "bp") e.bp<BP_STORE>(e.g.p, e.scratch.p);
+        else if (nm == "bp_sirt") e.bp<BP_SIRT_UPD>(e.r.p, e.yk.p);
+        else if (nm == "sirt") e.sirt_step(e.yk.p);
+        else if (nm == "fgp_sweep") { fgp_sweep_kernel<false><<<gsw, TV_WARPS * 32, 0, e.st>>>(fp); ++e.launches; }
+        else if (nm == "fgp_first") { fgp_sweep_kernel<true><<<gsw, TV_WARPS * 32, 0, e.st>>>(fp); ++e.launches; }
+        else if (nm == "fgp_final") { fgp_final_kernel<<<dim3(gsw.x, (e.N + 7) / 8, e.nxb), 256, 0, e.st>>>(fp, e.scratch.p); ++e.launches; }
+        else if (nm == "tv") { tv_value_kernel<<<(unsigned)((rows + 7) / 8), 256, 0, e.st>>>(e.recon.p, e.dims(), nullptr, e.d_red); ++e.launches; }
+        else if (nm == "momentum") { momentum_kernel<<<ew_blocks(n / 4), 256, 0, e.st>>>(reinterpret_cast<float4*>(e.scratch.p), reinterpret_cast<float4*>(e.yk.p), reinterpret_cast<float4*>(e.recon_old.p), 0.5f, n / 4); ++e.launches; }
+        else if (nm == "tvgd_grad") { tvgd_gradient_kernel<<<dim3(gsw.x, (e.N + 7) / 8, e.nxb), 256, 0, e.st>>>(gp); ++e.launches; }
+        else if (nm == "tvgd_update") { tvgd_update_kernel<<<ew_blocks(n / 4), 256, 0, e.st>>>(e.yk.p, e.scratch.p, e.d_red + 1, 0.f, 0, n / 4); ++e.launches; }
+        else if (nm == "sqdist") { reduce_kernel<RED_SQDIST><<<ew_blocks(n / 4), 256, 0, e.st>>>(reinterpret_cast<const float4*>(e.recon.p), reinterpret_cast<const float4*>(e.yk.p), n / 4, e.d_red + 2); ++e.launches; }
+        else throw CudaError("ttv_time_kernel: unknown kernel name '" + nm + "'");
+    };
+    (void)arg_i; (void)arg_f;
+    cudaEvent_t a, b;
+    TTV_CUDA(cudaEventCreate(&a)); TTV_CUDA(cudaEventCreate(&b));
+    one(); e.sync();
+    TTV_CUDA(cudaEventRecord(a, e.st));
+    for (int i = 0; i < reps; ++i) one();
+    TTV_CUDA(cudaEventRecord(b, e.st));
+    TTV_CUDA(cudaEventSynchronize(b));
+    TTV_LAUNCH_CHECK();
+    float t = 0; TTV_CUDA(cudaEventElapsedTime(&t, a, b));
+    cudaEventDestroy(a); cudaEventDestroy(b);
+    *ms = t / (reps > 0 ? reps : 1);
+    TTV_CATCH
+}
+
+}  // extern "C"

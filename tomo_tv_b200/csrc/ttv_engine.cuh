@@ -1,0 +1,582 @@
+// Device-resident reconstruction engine: the state machine of the reference's `tomoengine`
+// (T/gpu/utils/tomoengine.hpp:44-72, tomoengine.cpp) re-designed for B200.
+//
+// The reference keeps every volume in host memory and crosses the PCIe boundary twice per slice per
+// operator; here all volumes / sinograms live in HBM in the x-interleaved layout (ttv_common.cuh),
+// every operator is one batched launch over all slices, and host<->device copies happen only at
+// the C-ABI data methods (set_tilt_series, get_recon, ...).
+#pragma once
+#include "ttv_common.cuh"
+#include "ttv_fp.cuh"
+#include "ttv_bp.cuh"
+#include "ttv_tv.cuh"
+#include "ttv_elem.cuh"
+#include <vector>
+#include <string>
+#include <algorithm>
+#include <random>
+#include <cstring>
+#include <dlfcn.h>
+
+namespace ttv {
+
+// ------------------------------------------------------------------------------------------
+// driver entry point for tensor-map creation (no link-time dependency on libcuda)
+// ------------------------------------------------------------------------------------------
+typedef CUresult (*PFN_encodeTiled)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*, const cuuint64_t*,
+                                    const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave, CUtensorMapSwizzle,
+                                    CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+inline PFN_encodeTiled get_encode_tiled() {
+    static PFN_encodeTiled fn = nullptr;
+    if (!fn) {
+        void* p = nullptr;
+        cudaDriverEntryPointQueryResult q;
+        TTV_CUDA(cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &p, cudaEnableDefault, &q));
+        if (!p || q != cudaDriverEntryPointSuccess) throw CudaError("cuTensorMapEncodeTiled entry point not available");
+        fn = reinterpret_cast<PFN_encodeTiled>(p);
+    }
+    return fn;
+}
+// 4-D map over an x-interleaved array [d3][d2][d1][32] of float32 with the given box.
+inline CUtensorMap make_tmap(const float* base, uint64_t d1, uint64_t d2, uint64_t d3, uint32_t b1, uint32_t b2) {
+    CUtensorMap tm;
+    cuuint64_t dims[4] = {32, d1, d2, d3};
+    cuuint64_t strides[3] = {128, 128 * d1, 128 * d1 * d2};
+    cuuint32_t box[4] = {32, b1, b2, 1};
+    cuuint32_t estr[4] = {1, 1, 1, 1};
+    CUresult r = get_encode_tiled()(&tm, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 4, const_cast<float*>(base), dims, strides, box, estr,
+                                    CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_NONE, CU_TENSOR_MAP_L2_PROMOTION_L2_128B,
+                                    CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    if (r != CUDA_SUCCESS) throw CudaError("cuTensorMapEncodeTiled failed (code " + std::to_string((int)r) + ")");
+    return tm;
+}
+
+// ------------------------------------------------------------------------------------------
+// NCCL through dlopen (only touched when ttv_comm_init is called)
+// ------------------------------------------------------------------------------------------
+struct Nccl {
+    typedef struct ncclComm* comm_t;
+    typedef struct { char internal[128]; } uid_t;
+    void* lib = nullptr;
+    int (*GetUniqueId)(uid_t*) = nullptr;
+    int (*CommInitRank)(comm_t*, int, uid_t, int) = nullptr;
+    int (*CommDestroy)(comm_t) = nullptr;
+    int (*AllReduce)(const void*, void*, size_t, int, int, comm_t, cudaStream_t) = nullptr;
+    int (*Send)(const void*, size_t, int, int, comm_t, cudaStream_t) = nullptr;
+    int (*Recv)(void*, size_t, int, int, comm_t, cudaStream_t) = nullptr;
+    int (*GroupStart)() = nullptr;
+    int (*GroupEnd)() = nullptr;
+    const char* (*GetErrorString)(int) = nullptr;
+    static Nccl& get() {
+        static Nccl n;
+        if (!n.lib) {
+            n.lib = dlopen("libnccl.so.2", RTLD_NOW | RTLD_GLOBAL);
+            if (!n.lib) n.lib = dlopen("libnccl.so", RTLD_NOW | RTLD_GLOBAL);
+            if (!n.lib) throw CudaError(std::string("cannot load NCCL: ") + dlerror());
+#define TTV_SYM(f) *(void**)(&n.f) = dlsym(n.lib, "nccl" #f); if (!n.f) throw CudaError("NCCL symbol nccl" #f " missing");
+            TTV_SYM(GetUniqueId) TTV_SYM(CommInitRank) TTV_SYM(CommDestroy) TTV_SYM(AllReduce) TTV_SYM(Send) TTV_SYM(Recv)
+            TTV_SYM(GroupStart) TTV_SYM(GroupEnd) TTV_SYM(GetErrorString)
+#undef TTV_SYM
+        }
+        return n;
+    }
+    void check(int r, const char* what) { if (r != 0) throw CudaError(std::string(what) + ": " + GetErrorString(r)); }
+    enum { Float32 = 7, Float64 = 8, Sum = 0, Max = 2 };
+};
+
+struct DBuf {
+    float* p = nullptr; size_t n = 0;
+    void alloc(size_t count) {
+        if (p && n == count) { TTV_CUDA(cudaMemset(p, 0, n * sizeof(float))); return; }
+        release();
+        TTV_CUDA(cudaMalloc(&p, count * sizeof(float))); n = count;
+        TTV_CUDA(cudaMemset(p, 0, n * sizeof(float)));
+    }
+    void release() { if (p) cudaFree(p); p = nullptr; n = 0; }
+    bool ok() const { return p != nullptr; }
+};
+
+class Engine {
+public:
+    int nx, N, Na = 0, nxb;          // local slices, Nray=Ny=Nz, angles, x-blocks
+    int xoff, nxg;                   // slab position in the global volume
+    int device, gpuID = -1;
+    cudaStream_t st = nullptr;
+    std::vector<AngleGeom> geom;
+    std::vector<float> angles;
+    long long launches = 0;
+
+    // FP plan
+    int* d_win0 = nullptr; FpAngle* d_fpang = nullptr; FpGroup* d_fpgrp = nullptr;
+    int fp_ngroups = 0, fp_ndg = 0, fp_CW = 0, fp_TR = 2, fp_S = 2; size_t fp_smem = 0;
+    float* d_theta = nullptr;
+
+    // state (x-interleaved)
+    DBuf recon, yk, recon_old, temp, original;
+    DBuf b, g, r;                    // measured / model / residual sinograms
+    DBuf P[6], scratch;              // FGP dual variables (ping-pong), D / gradient scratch
+    DBuf R, C;                       // SIRT weights
+    DBuf stage;                      // host I/O staging (reference layout, one x-block)
+    DBuf planes;                     // halo planes
+    double* d_red = nullptr;         // reduction slots
+    int* d_imax = nullptr;
+
+    bool momentum = false, weights_ready = false, sart_ready = false, fp_ready = false, kl_ready = false;
+    float sart_relax = 1.0f; std::string projOrder = "sequential", fbpFilter;
+    std::vector<int> sart_order;
+    float L_A = 0.f, L_Aml = 0.f;
+
+    // comm
+    Nccl::comm_t comm = nullptr; int rank = 0, nranks = 1;
+
+    Engine(int nslice, int nray, const float* ang, int nang, int dev, int x_offset, int nslice_global)
+        : nx(nslice), N(nray), xoff(x_offset), nxg(nslice_global)
+    {
+        if (nslice <= 0 || nray <= 0) throw CudaError("tomoengine: Nslice and Nray must be positive");
+        int cnt = 0;
+        cudaError_t e = cudaGetDeviceCount(&cnt);
+        if (e != cudaSuccess || cnt == 0) throw CudaError("An Nvidia GPU is needed: no CUDA device available (no CPU fallback)");
+        if (dev < 0) TTV_CUDA(cudaGetDevice(&dev));
+        device = dev;
+        TTV_CUDA(cudaSetDevice(device));
+        TTV_CUDA(cudaStreamCreateWithFlags(&st, cudaStreamNonBlocking));
+        nxb = (nx + 31) / 32;
+        recon.alloc(vol_elems());
+        TTV_CUDA(cudaMalloc(&d_red, 16 * sizeof(double)));
+        TTV_CUDA(cudaMalloc(&d_imax, sizeof(int)));
+        size_t stage_elems = (size_t)32 * std::max<size_t>((size_t)N * N, 1);
+        stage.alloc(stage_elems);
+        if (nang > 0) set_angles(ang, nang);
+    }
+    ~Engine() {
+        cudaSetDevice(device);
+        if (comm) Nccl::get().CommDestroy(comm);
+        for (DBuf* d : {&recon, &yk, &recon_old, &temp, &original, &b, &g, &r, &scratch, &R, &C, &stage, &planes}) d->release();
+        for (auto& d : P) d.release();
+        cudaFree(d_win0); cudaFree(d_fpang); cudaFree(d_fpgrp); cudaFree(d_theta); cudaFree(d_red); cudaFree(d_imax);
+        if (st) cudaStreamDestroy(st);
+    }
+
+    size_t vol_elems() const { return (size_t)nxb * N * N * 32; }
+    size_t sino_elems() const { return (size_t)nxb * Na * N * 32; }
+    VolDims dims() const { return VolDims{nx, nxb, N, xoff, nxg}; }
+    void use() { TTV_CUDA(cudaSetDevice(device)); }
+    void sync() { TTV_CUDA(cudaStreamSynchronize(st)); }
+
+    // ---------------------------------------------------------------------------------------
+    // geometry (A/src/GeometryUtil2D.cpp:35-74,107-130; A/cuda/2d/par_bp.cu:173-179)
+    // ---------------------------------------------------------------------------------------
+    void set_angles(const float* ang, int nang) {
+        use();
+        if (nang <= 0) throw CudaError("need at least one projection angle");
+        if (nang > BP_MAX_ANGLES) throw CudaError("more than 2048 projection angles are not supported yet");
+        Na = nang;
+        angles.assign(ang, ang + nang);
+        geom.resize(Na);
+        for (int i = 0; i < Na; ++i) {
+            const double al = (double)angles[i], c = std::cos(al), s = std::sin(al);
+            const float bDetSX = (float)(N * 1.0 * -0.5f);
+            const float rayX = (float)(0.0 * c - 1.0 * s), rayY = (float)(0.0 * s + 1.0 * c);
+            const float detSX = (float)((double)bDetSX * c), detSY = (float)((double)bDetSX * s);
+            const float detUX = (float)(1.0 * c), detUY = (float)(1.0 * s);
+            AngleGeom& q = geom[i];
+            q.rayX = rayX; q.rayY = rayY;
+            q.vertical = std::fabs(rayX) <= std::fabs(rayY) ? 1 : 0;
+            double ux = detUX, uy = detUY;
+            const double t = (ux * rayX + uy * rayY) / ((double)rayX * rayX + (double)rayY * rayY);
+            ux -= t * rayX; uy -= t * rayY;
+            const double n2 = uy * uy + ux * ux;
+            q.theta = (float)std::atan2(uy, ux);
+            q.detsize = (float)std::sqrt(n2);
+            q.offset = (float)(-0.5 * N - ((double)detSY * uy + (double)detSX * ux) / n2);
+            const double d = (double)detUX * rayY - (double)detUY * rayX;
+            q.sc = (float)(rayY / d);
+            q.ss = (float)(-rayX / d);
+            q.off = (float)(((double)detSY * rayX - (double)detSX * rayY) / d);
+            q.scale = (float)(std::sqrt((double)rayX * rayX + (double)rayY * rayY) / std::fabs(d));
+        }
+        // BP constants -> __constant__
+        std::vector<float4> kb(Na);
+        for (int i = 0; i < Na; ++i) kb[i] = make_float4(geom[i].sc, geom[i].ss, geom[i].off, geom[i].scale);
+        TTV_CUDA(cudaMemcpyToSymbolAsync(c_bp_angle, kb.data(), Na * sizeof(float4), 0, cudaMemcpyHostToDevice, st));
+        sync();
+        build_fp_plan();
+        b.alloc(sino_elems()); g.alloc(sino_elems()); r.release();
+        size_t stage_elems = (size_t)32 * std::max((size_t)N * N, (size_t)Na * N);
+        if (stage.n < stage_elems) stage.alloc(stage_elems);
+        weights_ready = false; sart_ready = false; kl_ready = false;
+    }
+
+    // angles sorted by (orientation, theta), groups of <= ag, per-line staging windows
+    void build_fp_plan() {
+        std::vector<int> vert, hori;
+        for (int i = 0; i < Na; ++i) (geom[i].vertical ? vert : hori).push_back(i);
+        auto by_theta = [&](int a, int c) { return geom[a].theta < geom[c].theta; };
+        std::sort(vert.begin(), vert.end(), by_theta);
+        std::sort(hori.begin(), hori.end(), by_theta);
+        const int ndg = (N + FP_DG - 1) / FP_DG;
+        const size_t budget = 200 * 1024;
+        int TR = 2;
+        for (int ag = FP_AG; ag >= 1; ag /= 2) {
+            std::vector<FpAngle> fa; std::vector<FpGroup> fg;
+            for (int pass = 0; pass < 2; ++pass) {
+                const std::vector<int>& lst = pass == 0 ? vert : hori;
+                for (size_t i = 0; i < lst.size(); i += ag) {
+                    FpGroup G; G.first = (int)fa.size(); G.count = (int)std::min<size_t>(ag, lst.size() - i); G.vertical = pass == 0; G.pad = 0;
+                    for (int k = 0; k < G.count; ++k) {
+                        const AngleGeom& q = geom[lst[i + k]];
+                        fa.push_back(FpAngle{q.theta, q.detsize, q.offset, lst[i + k]});
+                    }
+                    fg.push_back(G);
+                }
+            }
+            const int nlines = ((N + TR - 1) / TR) * TR;
+            std::vector<int> win((size_t)fg.size() * ndg * nlines);
+            int CW = 0;
+            for (size_t gi = 0; gi < fg.size(); ++gi) {
+                for (int dgi = 0; dgi < ndg; ++dgi) {
+                    const int dlo = dgi * FP_DG, dhi = std::min(dlo + FP_DG - 1, N - 1);
+                    for (int line = 0; line < nlines; ++line) {
+                        double pmin = 1e30, pmax = -1e30;
+                        for (int k = 0; k < fg[gi].count; ++k) {
+                            const FpAngle& A = fa[fg[gi].first + k];
+                            const double c = std::cos((double)A.theta), s = std::sin((double)A.theta);
+                            double detStep, step;
+                            if (fg[gi].vertical) { detStep = A.detsize / c; step = s / c; }
+                            else { detStep = -A.detsize / s; step = c / s; }
+                            for (int d : {dlo, dhi}) {
+                                const double pp = (d - 0.5 * N + 0.5 - A.offset) * detStep + (line - 0.5 * N + 0.5) * step + 0.5 * N;
+                                pmin = std::min(pmin, pp); pmax = std::max(pmax, pp);
+                            }
+                        }
+                        const int w0 = (int)std::floor(pmin - 0.5) - 1;
+                        const int wend = (int)std::floor(pmax - 0.5) + 3;
+                        win[(gi * ndg + dgi) * nlines + line] = w0;
+                        CW = std::max(CW, wend - w0 + 1);
+                    }
+                }
+            }
+            if (CW > 256 && ag > 1) continue;
+            if (CW > 256) throw CudaError("forward-projector window exceeds the TMA box limit");
+            size_t stage_b = (size_t)TR * CW * 128;
+            int S = (int)std::min<size_t>(FP_MAX_STAGES, budget / stage_b);
+            if (S < 2) { TR = 1; stage_b = (size_t)CW * 128; S = (int)std::min<size_t>(FP_MAX_STAGES, budget / stage_b); }
+            fp_CW = CW; fp_TR = TR; fp_S = S; fp_ngroups = (int)fg.size(); fp_ndg = ndg;
+            fp_smem = (size_t)S * stage_b + (size_t)(S * TR + 1) * sizeof(float) + 2 * S * sizeof(uint64_t) + 16;
+            if (TR == 1) {   // rebuild the table with nlines = N
+                std::vector<int> w1((size_t)fg.size() * ndg * N);
+                for (size_t q = 0; q < fg.size() * (size_t)ndg; ++q)
+                    for (int line = 0; line < N; ++line) w1[q * N + line] = win[q * nlines + line];
+                win.swap(w1);
+            }
+            cudaFree(d_win0); cudaFree(d_fpang); cudaFree(d_fpgrp); cudaFree(d_theta);
+            TTV_CUDA(cudaMalloc(&d_win0, win.size() * sizeof(int)));
+            TTV_CUDA(cudaMalloc(&d_fpang, fa.size() * sizeof(FpAngle)));
+            TTV_CUDA(cudaMalloc(&d_fpgrp, fg.size() * sizeof(FpGroup)));
+            TTV_CUDA(cudaMalloc(&d_theta, Na * sizeof(float)));
+            TTV_CUDA(cudaMemcpy(d_win0, win.data(), win.size() * sizeof(int), cudaMemcpyHostToDevice));
+            TTV_CUDA(cudaMemcpy(d_fpang, fa.data(), fa.size() * sizeof(FpAngle), cudaMemcpyHostToDevice));
+            TTV_CUDA(cudaMemcpy(d_fpgrp, fg.data(), fg.size() * sizeof(FpGroup), cudaMemcpyHostToDevice));
+            std::vector<float> th(Na);
+            for (int i = 0; i < Na; ++i) th[i] = geom[i].theta;
+            TTV_CUDA(cudaMemcpy(d_theta, th.data(), Na * sizeof(float), cudaMemcpyHostToDevice));
+            set_fp_attrs();
+            return;
+        }
+    }
+    template <int EPI> void fp_attr() {
+        TTV_CUDA(cudaFuncSetAttribute(fp_kernel<EPI>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)fp_smem));
+    }
+    void set_fp_attrs() {
+        fp_attr<FP_STORE>(); fp_attr<FP_SIRT_RES>(); fp_attr<FP_KL>(); fp_attr<FP_STORE_DIST>(); fp_attr<FP_RESID>();
+        TTV_CUDA(cudaFuncSetAttribute(bp_kernel<BP_STORE>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)BP_SMEM));
+        TTV_CUDA(cudaFuncSetAttribute(bp_kernel<BP_SIRT_UPD>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)BP_SMEM));
+        TTV_CUDA(cudaFuncSetAttribute(bp_kernel<BP_STEP_UPD>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)BP_SMEM));
+        TTV_CUDA(cudaFuncSetAttribute(bp_kernel<BP_ADD>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)BP_SMEM));
+    }
+
+    void need_angles() const { if (Na <= 0) throw CudaError("projection angles were not set (construct with angles or call update_projection_angles)"); }
+
+    // ---------------------------------------------------------------------------------------
+    // operators (batched over all local slices)
+    // ---------------------------------------------------------------------------------------
+    template <int EPI>
+    void fp(const float* vol, float* out, const float* bmeas, double* red, int nblocks = -1, float eps = 0.1f) {
+        need_angles();
+        const int zb = nblocks < 0 ? nxb : nblocks;
+        CUtensorMap tmV = make_tmap(vol, N, N, zb, fp_CW, 1);
+        CUtensorMap tmH = make_tmap(vol, N, N, zb, 1, fp_CW);
+        FpParams p;
+        p.ang = d_fpang; p.grp = d_fpgrp; p.win0 = d_win0;
+        p.N = N; p.Nd = N; p.Na = Na; p.ndg = fp_ndg; p.CW = fp_CW; p.TR = fp_TR; p.S = fp_S;
+        p.out = out; p.b = bmeas; p.R = R.p; p.red = red; p.eps = eps;
+        dim3 grid(fp_ndg, fp_ngroups, zb);
+        fp_kernel<EPI><<<grid, FP_THREADS, fp_smem, st>>>(tmV, tmH, p);
+        TTV_LAUNCH_CHECK(); ++launches;
+    }
+    template <int EPI>
+    void bp(const float* sino, float* vol, float step = 0.f, int nblocks = -1) {
+        need_angles();
+        const int zb = nblocks < 0 ? nxb : nblocks;
+        CUtensorMap tmS = make_tmap(sino, N, Na, zb, BP_CW, 1);
+        BpParams p; p.N = N; p.Nd = N; p.Na = Na; p.vol = vol; p.C = C.p; p.step = step;
+        const int nt = (N + BP_TILE - 1) / BP_TILE;
+        dim3 grid(nt, nt, zb);
+        bp_kernel<EPI><<<grid, BP_THREADS, BP_SMEM, st>>>(tmS, p);
+        TTV_LAUNCH_CHECK(); ++launches;
+    }
+
+    double read_red(int slot) {
+        double v; TTV_CUDA(cudaMemcpyAsync(&v, d_red + slot, sizeof(double), cudaMemcpyDeviceToHost, st)); sync();
+        return allreduce_sum(v);
+    }
+    void zero_red(int slot) { TTV_CUDA(cudaMemsetAsync(d_red + slot, 0, sizeof(double), st)); }
+
+    double allreduce_sum(double v) {
+        if (nranks <= 1) return v;
+        // host scalar -> device slot 15 -> all-reduce -> host
+        TTV_CUDA(cudaMemcpyAsync(d_red + 15, &v, sizeof(double), cudaMemcpyHostToDevice, st));
+        Nccl& n = Nccl::get();
+        n.check(n.AllReduce(d_red + 15, d_red + 15, 1, Nccl::Float64, Nccl::Sum, comm, st), "ncclAllReduce");
+        TTV_CUDA(cudaMemcpyAsync(&v, d_red + 15, sizeof(double), cudaMemcpyDeviceToHost, st)); sync();
+        return v;
+    }
+
+    // R = inv(FP(1)), C = inv(BP(1)), L = max(BP(FP(1)))      A/cuda/2d/sirt.cu:112-147; tomoengine.cpp:370-371
+    void compute_weights() {
+        if (weights_ready) return;
+        need_angles();
+        const size_t nv1 = (size_t)N * N * 32, ns1 = (size_t)Na * N * 32;
+        DBuf v1, s1, plane;
+        v1.alloc(nv1); s1.alloc(ns1);
+        R.alloc((size_t)Na * N); C.alloc((size_t)N * N);
+        // FP of ones (only slice 0 of the single block is populated)
+        fill_valid_kernel<<<1024, 256, 0, st>>>(v1.p, 1.0f, 1, (int64_t)N * N, 1); ++launches;
+        fp<FP_STORE>(v1.p, s1.p, nullptr, nullptr, 1);
+        gather_slice_kernel<<<256, 256, 0, st>>>(s1.p, R.p, 0, (int64_t)Na * N); ++launches;
+        // L = max(BP(FP(1)))
+        bp<BP_STORE>(s1.p, v1.p, 0.f, 1);
+        gather_slice_kernel<<<256, 256, 0, st>>>(v1.p, C.p, 0, (int64_t)N * N); ++launches;
+        std::vector<float> h((size_t)N * N);
+        TTV_CUDA(cudaMemcpyAsync(h.data(), C.p, h.size() * sizeof(float), cudaMemcpyDeviceToHost, st)); sync();
+        L_A = *std::max_element(h.begin(), h.end());
+        // C = inv(BP(ones sinogram))
+        fill_valid_kernel<<<1024, 256, 0, st>>>(s1.p, 1.0f, 1, (int64_t)Na * N, 1); ++launches;
+        bp<BP_STORE>(s1.p, v1.p, 0.f, 1);
+        gather_slice_kernel<<<256, 256, 0, st>>>(v1.p, C.p, 0, (int64_t)N * N); ++launches;
+        // opInvert (A/cuda/2d/arith.cu:94-101) on the host: tiny 2-D arrays
+        std::vector<float> hr((size_t)Na * N);
+        TTV_CUDA(cudaMemcpyAsync(hr.data(), R.p, hr.size() * sizeof(float), cudaMemcpyDeviceToHost, st));
+        TTV_CUDA(cudaMemcpyAsync(h.data(), C.p, h.size() * sizeof(float), cudaMemcpyDeviceToHost, st)); sync();
+        for (auto& x : hr) x = x > 0.000001f ? 1.0f / x : 0.0f;
+        for (auto& x : h) x = x > 0.000001f ? 1.0f / x : 0.0f;
+        TTV_CUDA(cudaMemcpyAsync(R.p, hr.data(), hr.size() * sizeof(float), cudaMemcpyHostToDevice, st));
+        TTV_CUDA(cudaMemcpyAsync(C.p, h.data(), h.size() * sizeof(float), cudaMemcpyHostToDevice, st)); sync();
+        v1.release(); s1.release();
+        weights_ready = true;
+    }
+
+    // one SIRT iteration on `vol`: r = (b - A vol) * R ; vol = max(vol + C * A^T r, 0)   (sirt.cu:237-277)
+    void sirt_step(float* vol) {
+        if (!r.ok()) r.alloc(sino_elems());
+        fp<FP_SIRT_RES>(vol, r.p, b.p, nullptr);
+        bp<BP_SIRT_UPD>(r.p, vol);
+    }
+
+    // ---------------------------------------------------------------------------------------
+    // host I/O in the reference layouts
+    // ---------------------------------------------------------------------------------------
+    void upload(DBuf& dst, const float* host, int64_t M) {        // host [nx][M]
+        use();
+        for (int xbk = 0; xbk < nxb; ++xbk) {
+            const int x0 = xbk * 32, cnt = std::min(32, nx - x0);
+            TTV_CUDA(cudaMemcpyAsync(stage.p, host + (size_t)x0 * M, (size_t)cnt * M * sizeof(float), cudaMemcpyHostToDevice, st));
+            dim3 grid((unsigned)((M + 31) / 32), 1);
+            pack_kernel<<<grid, 256, 0, st>>>(stage.p, dst.p + (size_t)xbk * M * 32, cnt, M, 0, cnt); ++launches;
+            TTV_LAUNCH_CHECK();
+            sync();   // staging buffer is reused
+        }
+    }
+    void download(const DBuf& src, float* host, int64_t M) {
+        use();
+        for (int xbk = 0; xbk < nxb; ++xbk) {
+            const int x0 = xbk * 32, cnt = std::min(32, nx - x0);
+            dim3 grid((unsigned)((M + 31) / 32), 1);
+            unpack_kernel<<<grid, 256, 0, st>>>(src.p + (size_t)xbk * M * 32, stage.p, cnt, M, 0, cnt); ++launches;
+            TTV_LAUNCH_CHECK();
+            TTV_CUDA(cudaMemcpyAsync(host + (size_t)x0 * M, stage.p, (size_t)cnt * M * sizeof(float), cudaMemcpyDeviceToHost, st));
+            sync();
+        }
+    }
+    void set_slice(DBuf& dst, const float* host, int s) {
+        if (s < 0 || s >= nx) throw CudaError("slice index out of range");
+        if (!dst.ok()) throw CudaError("volume was not initialised");
+        use();
+        const int64_t M = (int64_t)N * N;
+        TTV_CUDA(cudaMemcpyAsync(stage.p, host, M * sizeof(float), cudaMemcpyHostToDevice, st));
+        scatter_slice_kernel<<<256, 256, 0, st>>>(dst.p, stage.p, s, M); ++launches;
+        sync();
+    }
+    void get_slice(const DBuf& src, float* host, int s) {
+        if (s < 0 || s >= nx) throw CudaError("slice index out of range");
+        use();
+        const int64_t M = (int64_t)N * N;
+        gather_slice_kernel<<<256, 256, 0, st>>>(src.p, stage.p, s, M); ++launches;
+        TTV_CUDA(cudaMemcpyAsync(host, stage.p, M * sizeof(float), cudaMemcpyDeviceToHost, st));
+        sync();
+    }
+
+    // ---------------------------------------------------------------------------------------
+    // halo planes (multi-GPU): ring / chain exchange of single slices over NCCL
+    // ---------------------------------------------------------------------------------------
+    float* plane(int i) {
+        const size_t M = (size_t)N * N;
+        if (planes.n < 12 * M) planes.alloc(12 * M);
+        return planes.p + (size_t)i * M;
+    }
+    // send slice `xs` of `src` to rank `to`, receive a plane from rank `from` (either may be -1)
+    void exchange(const float* src, int xs, int to, float* sendbuf, int from, float* recvbuf) {
+        Nccl& n = Nccl::get();
+        const int64_t M = (int64_t)N * N;
+        if (to >= 0) { gather_slice_kernel<<<256, 256, 0, st>>>(src, sendbuf, xs, M); ++launches; }
+        n.check(n.GroupStart(), "ncclGroupStart");
+        if (to >= 0) n.check(n.Send(sendbuf, M, Nccl::Float32, to, comm, st), "ncclSend");
+        if (from >= 0) n.check(n.Recv(recvbuf, M, Nccl::Float32, from, comm, st), "ncclRecv");
+        n.check(n.GroupEnd(), "ncclGroupEnd");
+    }
+
+    // ---------------------------------------------------------------------------------------
+    // regularisers
+    // ---------------------------------------------------------------------------------------
+    double tv_value(const float* v) {
+        const float* hn = nullptr;
+        if (nranks > 1) {   // periodic ring: my slice 0 goes to the previous rank, I receive the next rank's slice 0
+            exchange(v, 0, (rank - 1 + nranks) % nranks, plane(0), (rank + 1) % nranks, plane(1));
+            hn = plane(1);
+        }
+        zero_red(0);
+        const int64_t rows = (int64_t)nxb * N;
+        tv_value_kernel<<<(unsigned)((rows + 7) / 8), 256, 0, st>>>(v, dims(), hn, d_red); ++launches;
+        TTV_LAUNCH_CHECK();
+        return read_red(0);
+    }
+
+    // cuda_tv_fgp_3D, tv_fgp.cu:192-281.  Returns TV of the input.
+    float tv_fgp(int iter, float lambda) {
+        use();
+        const size_t n = vol_elems();
+        const float tv0 = (float)tv_value(recon.p);
+        if (!scratch.ok()) scratch.alloc(n);
+        dim3 grid((N + TV_KSEG - 1) / TV_KSEG, (N + TV_WARPS - 1) / TV_WARPS, nxb);
+        if (iter <= 0) {
+            const float* hn = nullptr;
+            if (nranks > 1) { exchange(recon.p, 0, (rank - 1 + nranks) % nranks, plane(0), (rank + 1) % nranks, plane(1)); hn = plane(1); }
+            const int64_t rows = (int64_t)nxb * N;
+            tv_map_kernel<<<(unsigned)((rows + 7) / 8), 256, 0, st>>>(recon.p, scratch.p, dims(), hn); ++launches;
+            std::swap(recon.p, scratch.p);
+            sync();
+            return tv0;
+        }
+        for (int i = 0; i < 6; ++i) if (!P[i].ok() && iter > 1) P[i].alloc(n);
+        FgpParams p;
+        p.in = recon.p; p.lambda = lambda; p.multip = 1.0f / (26.0f * lambda); p.d = dims();
+        p.hl_P1 = p.hr_in = p.hr_P1 = p.hr_P2 = p.hr_P3 = nullptr;
+        const bool has_left = nranks > 1 && rank > 0, has_right = nranks > 1 && rank < nranks - 1;
+        if (nranks > 1) {
+            // `in` boundary slice is constant over the sweeps: one exchange (chain, non-periodic)
+            exchange(recon.p, 0, has_left ? rank - 1 : -1, plane(2), has_right ? rank + 1 : -1, plane(3));
+            if (has_right) p.hr_in = plane(3);
+        }
+        int cur = 0;   // P[cur*3 ..] holds the current dual variable
+        for (int it = 0; it < iter; ++it) {
+            const bool first = (it == 0), last = (it == iter - 1);
+            if (!first) {
+                p.P1 = P[cur * 3 + 0].p; p.P2 = P[cur * 3 + 1].p; p.P3 = P[cur * 3 + 2].p;
+                if (nranks > 1) {
+                    // P1 of my last slice -> right neighbour (its x-1); P1..P3 of my first slice -> left neighbour (its x+1)
+                    exchange(p.P1, nx - 1, has_right ? rank + 1 : -1, plane(4), has_left ? rank - 1 : -1, plane(5));
+                    exchange(p.P1, 0, has_left ? rank - 1 : -1, plane(6), has_right ? rank + 1 : -1, plane(7));
+                    exchange(p.P2, 0, has_left ? rank - 1 : -1, plane(8), has_right ? rank + 1 : -1, plane(9));
+                    exchange(p.P3, 0, has_left ? rank - 1 : -1, plane(10), has_right ? rank + 1 : -1, plane(11));
+                    p.hl_P1 = has_left ? plane(5) : nullptr;
+                    if (has_right) { p.hr_P1 = plane(7); p.hr_P2 = plane(9); p.hr_P3 = plane(11); }
+                }
+            } else { p.P1 = p.P2 = p.P3 = nullptr; }
+            if (last) {
+                dim3 g2((N + TV_KSEG - 1) / TV_KSEG, (N + 7) / 8, nxb);
+                fgp_final_kernel<<<g2, 256, 0, st>>>(p, scratch.p); ++launches;
+            } else {
+                const int nxt = first ? 0 : 1 - cur;
+                p.Q1 = P[nxt * 3 + 0].p; p.Q2 = P[nxt * 3 + 1].p; p.Q3 = P[nxt * 3 + 2].p;
+                if (first) fgp_sweep_kernel<true><<<grid, TV_WARPS * 32, 0, st>>>(p);
+                else fgp_sweep_kernel<false><<<grid, TV_WARPS * 32, 0, st>>>(p);
+                ++launches;
+                cur = nxt;
+            }
+            TTV_LAUNCH_CHECK();
+        }
+        std::swap(recon.p, scratch.p);   // the volume is replaced by the last D (tv_fgp.cu:272)
+        sync();
+        return tv0;
+    }
+
+    // cuda_tv_gd_3D, tv_gd.cu:141-218.  Returns TV of the input.
+    float tv_gd(int ng, float dPOCS) {
+        use();
+        const size_t n = vol_elems();
+        const float tv0 = (float)tv_value(recon.p);
+        if (!scratch.ok()) scratch.alloc(n);
+        dim3 grid((N + TV_KSEG - 1) / TV_KSEG, (N + 7) / 8, nxb);
+        for (int it = 0; it < ng; ++it) {
+            GdParams p; p.x = recon.p; p.g = scratch.p; p.hm = p.hp = nullptr; p.sumsq = d_red + 1; p.d = dims();
+            if (nranks > 1) {
+                exchange(recon.p, nx - 1, (rank + 1) % nranks, plane(0), (rank - 1 + nranks) % nranks, plane(1));
+                exchange(recon.p, 0, (rank - 1 + nranks) % nranks, plane(2), (rank + 1) % nranks, plane(3));
+                p.hm = plane(1); p.hp = plane(3);
+            }
+            zero_red(1);
+            tvgd_gradient_kernel<<<grid, 256, 0, st>>>(p); ++launches;
+            TTV_LAUNCH_CHECK();
+            if (nranks > 1) {
+                Nccl& nc = Nccl::get();
+                nc.check(nc.AllReduce(d_red + 1, d_red + 1, 1, Nccl::Float64, Nccl::Sum, comm, st), "ncclAllReduce");
+            }
+            tvgd_update_kernel<<<ew_blocks(n / 4), 256, 0, st>>>(recon.p, scratch.p, d_red + 1, dPOCS, it == ng - 1 ? 1 : 0, n / 4); ++launches;
+            TTV_LAUNCH_CHECK();
+        }
+        if (ng <= 0) { ew_kernel<EW_POS><<<ew_blocks(n / 4), 256, 0, st>>>(reinterpret_cast<float4*>(recon.p), 0.f, n / 4); ++launches; }
+        sync();
+        return tv0;
+    }
+
+    template <int OP> double reduce(const float* a, const float* bb, size_t n) {
+        zero_red(2);
+        reduce_kernel<OP><<<ew_blocks(n / 4), 256, 0, st>>>(reinterpret_cast<const float4*>(a), reinterpret_cast<const float4*>(bb), n / 4, d_red + 2);
+        ++launches; TTV_LAUNCH_CHECK();
+        return read_red(2);
+    }
+    float max_of(const float* a, size_t n) {
+        const int init = float_ordered_host(-INFINITY);
+        TTV_CUDA(cudaMemcpyAsync(d_imax, &init, sizeof(int), cudaMemcpyHostToDevice, st));
+        max_kernel<<<ew_blocks(n / 4), 256, 0, st>>>(reinterpret_cast<const float4*>(a), n / 4, d_imax); ++launches;
+        int r2; TTV_CUDA(cudaMemcpyAsync(&r2, d_imax, sizeof(int), cudaMemcpyDeviceToHost, st)); sync();
+        int bits = r2 >= 0 ? r2 : r2 ^ 0x7FFFFFFF;
+        float f; std::memcpy(&f, &bits, 4);
+        if (nranks > 1) {
+            float* slot = reinterpret_cast<float*>(d_red + 14);
+            TTV_CUDA(cudaMemcpyAsync(slot, &f, sizeof(float), cudaMemcpyHostToDevice, st));
+            Nccl& nc = Nccl::get();
+            nc.check(nc.AllReduce(slot, slot, 1, Nccl::Float32, Nccl::Max, comm, st), "ncclAllReduce");
+            TTV_CUDA(cudaMemcpyAsync(&f, slot, sizeof(float), cudaMemcpyDeviceToHost, st)); sync();
+        }
+        return f;
+    }
+    static int float_ordered_host(float f) { int i; std::memcpy(&i, &f, 4); return i >= 0 ? i : i ^ 0x7FFFFFFF; }
+
+    // ---------------------------------------------------------------------------------------
+    // SART (A/cuda/2d/sart.cu:175-227): implemented in ttv_sart.cuh
+    // ---------------------------------------------------------------------------------------
+    void sart_pass(float beta, int niter);
+};
+
+}  // namespace ttv

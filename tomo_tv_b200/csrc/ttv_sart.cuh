@@ -1,0 +1,121 @@
+// SART: one projection angle at a time (A/cuda/2d/sart.cu:175-227).
+//   p = (b_a - FP_a x) * R_a                       callFP_SART :256-271 + MUL_SART :44-50
+//   x = max(x + beta * BP_a^{clamp}(p), 0)         devBP_SART, A/cuda/2d/par_bp.cu:139-159 (Clamp addressing, :269)
+// The sub-iterations are sequentially dependent, so each is a pair of whole-volume launches that
+// read cells straight from global memory / L2 (a single angle has no reuse worth staging).
+#pragma once
+#include "ttv_engine.cuh"
+
+namespace ttv {
+
+struct Sart1Params {
+    const float* vol; const float* b; const float* R; float* proj;   // proj: [xb][Nd][32]
+    float theta, detsize, offset; int vertical;
+    int a, N, Nd, Na;
+};
+
+// block = 8 warps; warp = 4 rays x 8 float4 lanes
+__global__ void __launch_bounds__(256) sart_fp1_kernel(const Sart1Params p)
+{
+    const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
+    const int lx = lane & 7, lr = lane >> 3;
+    const int d = (blockIdx.x * 8 + w) * 4 + lr;
+    const int xb = blockIdx.y;
+    const int N = p.N;
+    if (d >= p.Nd) return;
+    const float cth = __cosf(p.theta), sth = __sinf(p.theta);
+    float detStep, step, corr1;
+    if (p.vertical) { detStep = p.detsize / cth; step = sth / cth; corr1 = (cth < 0.0f) ? -1.0f / cth : 1.0f / cth; }
+    else { detStep = -p.detsize / sth; step = cth / sth; corr1 = (sth > 0.0f) ? 1.0f / sth : -1.0f / sth; }
+    const float t1 = __fadd_rn(__fadd_rn(__fmaf_rn((float)p.Nd, -0.5f, (float)d), 0.5f), -p.offset);
+    const float m = __fmul_rn(t1, detStep);
+    const float* base = p.vol + (size_t)xb * N * N * 32 + lx * 4;
+    // stride between consecutive cells along the interpolation axis / along the line axis
+    const int64_t s_interp = p.vertical ? 32 : (int64_t)N * 32;
+    const int64_t s_line = p.vertical ? (int64_t)N * 32 : 32;
+    float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
+    float fP = 0.f;
+    for (int line = 0; line < N; ++line) {
+        if ((line & 63) == 0) {
+            const float t2 = __fadd_rn(__fmaf_rn((float)N, -0.5f, (float)line), 0.5f);
+            float f = __fmaf_rn(t2, step, m);
+            f = __fmaf_rn((float)N, 0.5f, f);
+            f = __fadd_rn(f, -0.5f);
+            fP = __fadd_rn(f, 0.5f);
+        } else fP = __fadd_rn(fP, step);
+        const int q = __float2int_rn(fP * 256.0f) - 128;
+        const int i = q >> 8;
+        const float w1 = (float)(q & 255), w0 = 256.0f - w1;
+        float4 v0 = make_float4(0.f, 0.f, 0.f, 0.f), v1 = v0;
+        const float* lp = base + line * s_line;
+        if (i >= 0 && i < N) v0 = *reinterpret_cast<const float4*>(lp + i * s_interp);
+        if (i + 1 >= 0 && i + 1 < N) v1 = *reinterpret_cast<const float4*>(lp + (i + 1) * s_interp);
+        acc.x = fmaf(w1, v1.x, fmaf(w0, v0.x, acc.x)); acc.y = fmaf(w1, v1.y, fmaf(w0, v0.y, acc.y));
+        acc.z = fmaf(w1, v1.z, fmaf(w0, v0.z, acc.z)); acc.w = fmaf(w1, v1.w, fmaf(w0, v0.w, acc.w));
+    }
+    const float cs = corr1 * (1.0f / 256.0f);
+    const float4 bb = *reinterpret_cast<const float4*>(p.b + (((size_t)xb * p.Na + p.a) * p.Nd + d) * 32 + lx * 4);
+    const float wgt = p.R[(size_t)p.a * p.Nd + d];
+    float4 r;
+    r.x = fmaf(acc.x, -cs, bb.x) * wgt; r.y = fmaf(acc.y, -cs, bb.y) * wgt;
+    r.z = fmaf(acc.z, -cs, bb.z) * wgt; r.w = fmaf(acc.w, -cs, bb.w) * wgt;
+    *reinterpret_cast<float4*>(p.proj + ((size_t)xb * p.Nd + d) * 32 + lx * 4) = r;
+}
+
+struct SartBpParams { float* vol; const float* proj; float sc, ss, off, relax; int N, Nd; };
+
+__global__ void __launch_bounds__(256) sart_bp1_kernel(const SartBpParams p)
+{
+    const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
+    const int lx = lane & 7, lr = lane >> 3;
+    const int N = p.N;
+    const int64_t v = ((int64_t)blockIdx.x * 8 + w) * 4 + lr;     // voxel index Y*N + X
+    const int xb = blockIdx.y;
+    if (v >= (int64_t)N * N) return;
+    const int Y = (int)(v / N), X = (int)(v % N);
+    const float fX = (float)X - 0.5f * (float)N + 0.5f, fY = (float)Y - 0.5f * (float)N + 0.5f;
+    const float fT = __fadd_rn(__fmaf_rn(fX, p.sc, -__fmul_rn(fY, p.ss)), p.off);
+    const int q = __float2int_rn(fT * 256.0f) - 128;
+    const int i = q >> 8;
+    const float w1 = (float)(q & 255) * (1.0f / 256.0f), w0 = 1.0f - w1;
+    const int i0 = min(max(i, 0), p.Nd - 1), i1 = min(max(i + 1, 0), p.Nd - 1);     // Clamp addressing
+    const float* pr = p.proj + (size_t)xb * p.Nd * 32 + lx * 4;
+    const float4 v0 = *reinterpret_cast<const float4*>(pr + (size_t)i0 * 32);
+    const float4 v1 = *reinterpret_cast<const float4*>(pr + (size_t)i1 * 32);
+    float* o = p.vol + (((size_t)xb * N + Y) * N + X) * 32 + lx * 4;
+    float4 x = *reinterpret_cast<float4*>(o);
+    x.x = fmaxf(fmaf(fmaf(w1, v1.x, w0 * v0.x), p.relax, x.x), 0.f);
+    x.y = fmaxf(fmaf(fmaf(w1, v1.y, w0 * v0.y), p.relax, x.y), 0.f);
+    x.z = fmaxf(fmaf(fmaf(w1, v1.z, w0 * v0.z), p.relax, x.z), 0.f);
+    x.w = fmaxf(fmaf(fmaf(w1, v1.w, w0 * v0.w), p.relax, x.w), 0.f);
+    *reinterpret_cast<float4*>(o) = x;
+}
+
+inline void Engine::sart_pass(float beta, int niter) {
+    need_angles();
+    if (!sart_ready) throw CudaError("SART called before initialize_SART");
+    if (beta != 1) sart_relax = beta;                           // sticky (tomoengine.cpp:172)
+    // projection order is re-drawn on every call (tomoengine.cpp:164, CudaSartAlgorithm.cpp:109-136)
+    sart_order.resize(Na);
+    for (int i = 0; i < Na; ++i) sart_order[i] = i;
+    if (projOrder == "random") {
+        for (int i = 0; i < Na - 1; ++i) { const int k = rand() % (Na - i); std::swap(sart_order[i], sart_order[i + k]); }
+    }
+    if (scratch.n < (size_t)nxb * N * 32) scratch.alloc(vol_elems());
+    float* proj = scratch.p;
+    dim3 gfp((N + 31) / 32, nxb), gbp((unsigned)(((int64_t)N * N + 31) / 32), nxb);
+    for (int it = 0; it < Na * niter; ++it) {
+        const int a = sart_order[it % Na];
+        Sart1Params f; f.vol = recon.p; f.b = b.p; f.R = R.p; f.proj = proj;
+        f.theta = geom[a].theta; f.detsize = geom[a].detsize; f.offset = geom[a].offset; f.vertical = geom[a].vertical;
+        f.a = a; f.N = N; f.Nd = N; f.Na = Na;
+        sart_fp1_kernel<<<gfp, 256, 0, st>>>(f); ++launches;
+        SartBpParams q; q.vol = recon.p; q.proj = proj; q.sc = geom[a].sc; q.ss = geom[a].ss; q.off = geom[a].off;
+        q.relax = sart_relax; q.N = N; q.Nd = N;
+        sart_bp1_kernel<<<gbp, 256, 0, st>>>(q); ++launches;
+    }
+    TTV_LAUNCH_CHECK();
+    sync();
+}
+
+}  // namespace ttv
