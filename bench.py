@@ -1,0 +1,306 @@
+#!/usr/bin/env python
+"""Headline benchmark: FISTA-TV iterations/s at 512^3 x 180 angles (BASELINE.json), 1..8 B200s.
+
+One step = one FISTA-TV iteration of the reference loop (tomofusion/gpu/reconstructor.py:137-148 with
+show_convergence=False): SIRT(1) on yk  +  tv_fgp(nTViter=10, lambda=0.1) on recon  +
+fista_momentum(beta_k), issued through the C ABI exactly as TomoGPU.fista issues them.
+
+  python bench.py [--gpus N] [--steps K] [--warmup W] [--size 512] [--angles 180]
+  python bench.py --impl reference ...      times the CPU restatement of the same iteration (oracle/,
+                                            OpenMP on all host cores) on a bounded slab of the workload
+
+N > 1: launched by torchrun, one process per GPU; the volume is sharded into contiguous x-slabs
+(strong scaling: the 512^3 job is fixed), TV halos and scalar norms go over NCCL.
+"""
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+METRIC = "fista_tv_iters_per_sec"
+UNIT = "iterations/s"
+LAMBDA, NTV = 0.1, 10
+
+
+def peaks():
+    try:
+        return json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json"))), "measured"
+    except Exception:
+        return {"hbm_gbs": 6650.0}, "fallback"
+
+
+class ClockSampler:
+    """nvidia-smi clocks / throttle reasons sampled DURING the timed region."""
+    Q = ("clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
+         "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index):
+        self.rows, self.proc, self.index = [], None, index
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", f"--id={self.index}", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits", "-lms", "100"],
+                                         stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            threading.Thread(target=self._read, daemon=True).start()
+        except Exception:
+            self.proc = None
+
+    def _read(self):
+        for line in self.proc.stdout:
+            self.rows.append([c.strip() for c in line.split(",")])
+
+    def stop(self):
+        if not self.proc:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        self.proc.terminate()
+        try:
+            self.proc.wait(timeout=2)
+        except Exception:
+            self.proc.kill()
+        sm = [float(r[0]) for r in self.rows if len(r) >= 7 and r[0].replace(".", "").isdigit()]
+        mx = [float(r[1]) for r in self.rows if len(r) >= 7 and r[1].replace(".", "").isdigit()]
+        pw = [float(r[2]) for r in self.rows if len(r) >= 7 and r[2].replace(".", "").isdigit()]
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        reasons = sorted({names[i] for r in self.rows if len(r) >= 7 for i in range(4) if r[3 + i].lower().startswith("active")})
+        return {"sm_mhz": float(np.median(sm)) if sm else None, "sm_max_mhz": max(mx) if mx else None,
+                "power_w_max": max(pw) if pw else None, "samples": len(sm), "reasons": reasons}
+
+
+def fista_iteration(eng, state):
+    """One FISTA-TV iteration through the reference-facing calls."""
+    eng.SIRT(1)
+    eng.tv_fgp(NTV, LAMBDA)
+    tk = 0.5 * (1.0 + np.sqrt(1.0 + 4.0 * state["t"] ** 2))
+    eng.fista_momentum((state["t"] - 1.0) / tk)
+    state["t"] = tk
+
+
+# ------------------------------------------------------------------------------------------------
+def cpu_fista_sample(n, na, nslab, steps, warmup):
+    """The same iteration on the CPU oracle (test infrastructure, timed here as the reported CPU
+    baseline) for a slab of `nslab` slices of the n^2 x na problem.  Returns seconds per iteration."""
+    import oracle as orc
+    from tomo_tv_b200.phantom import phantom3d, tilt_angles_deg
+    ang = np.deg2rad(tilt_angles_deg(na)).astype(np.float32)
+    o = orc.Oracle(nslab, n, ang, quant=1)
+    o.recon[:] = phantom3d(nslab, n)
+    o.forward_projection()
+    o.set_tilt_series(o.g)
+    o.initialize_fista(); o.restart_recon()
+    st = {"t": 1.0}
+    for _ in range(warmup):
+        fista_iteration(o, st)
+    t0 = time.perf_counter()
+    for _ in range(steps):
+        fista_iteration(o, st)
+    return (time.perf_counter() - t0) / max(steps, 1), orc.lib().orc_num_threads()
+
+
+def run_reference(args):
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
+    cores = os.cpu_count() or 1
+    nslab = max(1, min(cores, args.size))
+    sec, threads = cpu_fista_sample(args.size, args.angles, nslab, args.steps, args.warmup)
+    value = (1.0 / sec) * (nslab / args.size)          # iterations/s of the FULL job at this per-slice rate
+    line = {
+        "impl": "reference", "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps,
+        "warmup": args.warmup, "ms_per_step": sec * 1e3 * (args.size / nslab), "higher_is_better": True, "scaling": "strong",
+        "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+        "config": {"workload": f"FISTA-TV {args.size}^3 x {args.angles} angles, nTViter={NTV}, lambda={LAMBDA}",
+                   "note": "reference GPU path needs CUDA; its CPU package (tomofusion/cpu) has no TV-FGP/FISTA, so the CPU arm is the "
+                           "oracle restatement of the same iteration (oracle/oracle.c, OpenMP over slices)"},
+        "cpu_baseline": {"value": value, "unit": UNIT, "cores": threads, "kind": "port",
+                         "sample": f"{nslab} of {args.size} slices of the {args.size}^2 x {args.angles} problem per step, scaled by {args.size}/{nslab}"},
+        "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "gpu_launches": 0,
+    }
+    print(json.dumps(line), flush=True)
+
+
+# ------------------------------------------------------------------------------------------------
+def run_ours(args):
+    import torch
+    import tomo_tv_b200 as ttv
+    from tomo_tv_b200.phantom import phantom3d, tilt_angles_deg, slab_bounds
+
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    rank = int(os.environ.get("RANK", "0"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py: no CUDA device (tomo_tv_b200 has no CPU fallback)")
+    torch.cuda.set_device(local)
+    dist = None
+    if world > 1:
+        import torch.distributed as dist
+        os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+
+    def barrier():
+        if dist is not None:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    def allmax(v):
+        if dist is None:
+            return v
+        t = torch.tensor([v], dtype=torch.float64, device="cuda")
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        return float(t.item())
+
+    def allsum(v):
+        if dist is None:
+            return v
+        t = torch.tensor([v], dtype=torch.float64, device="cuda")
+        dist.all_reduce(t, op=dist.ReduceOp.SUM)
+        return float(t.item())
+
+    n, na = args.size, args.angles
+    x0, nloc = slab_bounds(n, world, rank)
+    ang = np.deg2rad(tilt_angles_deg(na)).astype(np.float32)
+    eng = ttv.tomoengine(nloc, n, ang, device=local, x_offset=x0, nslice_global=n)
+    if world > 1:
+        uid = [ttv.tomoengine.nccl_unique_id() if rank == 0 else None]
+        dist.broadcast_object_list(uid, src=0)
+        eng.comm_init(uid[0], rank, world)
+
+    # synthetic data: phantom slab -> tilt series by the engine's own forward projector
+    vol = phantom3d(n, n, x0=x0, count=nloc)
+    eng.initialize_initial_volume()
+    eng.set_original_volume_all(vol)
+    eng.create_projections()
+    # pinned host buffers for the end-to-end leg
+    b_host = torch.empty((nloc, na * n), dtype=torch.float32, pin_memory=True)
+    b_np = b_host.numpy()
+    b_np[:] = eng.get_projections()
+    out_host = torch.empty((nloc, n, n), dtype=torch.float32, pin_memory=True)
+    out_np = out_host.numpy()
+    del vol
+
+    V, S, samples = eng.sizes()           # bytes of the local volume / sinogram slab
+    eng.initialize_fista(); eng.initialize_FP(); eng.restart_recon()
+    st = {"t": 1.0}
+    for _ in range(max(args.warmup, 3)):
+        fista_iteration(eng, st)
+
+    # ---------------- device-resident timed region ----------------
+    clocks = ClockSampler(local)
+    barrier()
+    if rank == 0:
+        clocks.start()
+    eng.profile(True)
+    l0 = eng.launch_count()
+    eng.timer_start()
+    for _ in range(args.steps):
+        fista_iteration(eng, st)
+    ms = eng.timer_stop()
+    barrier()
+    launches = eng.launch_count() - l0
+    prof = eng.profile_report()
+    eng.profile(False)
+    clk = clocks.stop() if rank == 0 else None
+    ms = allmax(ms)
+    launches = int(allsum(launches))
+    ms_per_step = ms / args.steps
+    value = 1e3 / ms_per_step
+
+    # ---------------- end-to-end leg: host buffers in, host volume out ----------------
+    barrier()
+    t0 = time.perf_counter()
+    eng.set_tilt_series(b_np)                                   # H2D from pinned memory (+ layout pack on device)
+    eng.restart_recon()
+    st2 = {"t": 1.0}
+    for _ in range(args.steps):
+        fista_iteration(eng, st2)                               # tv_fgp returns the TV scalar to the host every step
+    eng.get_recon_all_into(out_np)                              # D2H into pinned memory
+    torch.cuda.synchronize()
+    e2e_s = allmax(time.perf_counter() - t0)
+    barrier()
+    e2e_value = args.steps / e2e_s
+
+    # ---------------- roofline of the dominant kernel ----------------
+    pk, pk_kind = peaks()
+    nvox = nloc * n * n
+    alg_bytes = {                                               # algorithmic bytes per launch
+        "fp": V + 2 * S,                                        # read x, read b, write residual (fused SIRT residual)
+        "bp": S + 2 * V,                                        # read residual, read x, write x (fused SIRT update)
+        "fgp_first": 4 * V, "fgp_sweep": 7 * V, "fgp_final": 5 * V, "tv": V, "momentum": 3 * V,
+    }
+    groups = {}
+    for g, (tot, cnt) in prof.items():
+        per = tot / cnt
+        ent = {"ms_per_launch": per, "launches_per_step": cnt / args.steps, "share_of_step": tot / ms if ms > 0 else None}
+        if g in alg_bytes:
+            ent["algorithmic_bytes"] = alg_bytes[g]
+            ent["achieved_gbs"] = alg_bytes[g] / (per * 1e-3) / 1e9
+            ent["frac_of_hbm_peak"] = ent["achieved_gbs"] / pk["hbm_gbs"]
+        if g in ("fp", "bp"):
+            ent["samples_per_s"] = samples / (per * 1e-3)
+        groups[g] = ent
+    dom = max(prof, key=lambda g: prof[g][0]) if prof else None
+    roof = None
+    if dom and dom in alg_bytes:
+        roof = {"kernel": dom, "bound": "hbm", "achieved": groups[dom]["achieved_gbs"], "peak": pk["hbm_gbs"], "unit": "GB/s",
+                "frac": groups[dom]["frac_of_hbm_peak"], "traffic": None, "peak_kind": pk_kind,
+                "algorithmic_bytes_per_launch": alg_bytes[dom]}
+    iter_bytes = world * (74 * V + 3 * S)
+    iter_roof = {"algorithmic_bytes_per_iteration": iter_bytes, "achieved_gbs": iter_bytes / (ms_per_step * 1e-3) / 1e9,
+                 "frac_of_hbm_peak_x_gpus": iter_bytes / (ms_per_step * 1e-3) / 1e9 / (pk["hbm_gbs"] * world)}
+
+    line = None
+    if rank == 0:
+        line = {
+            "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": max(args.warmup, 3),
+            "ms_per_step": ms_per_step, "higher_is_better": True, "scaling": "strong", "vs_baseline": None,
+            "dtype": "f32", "data": "synthetic",
+            "config": {"workload": f"FISTA-TV {n}^3 x {na} angles, nTViter={NTV}, lambda={LAMBDA}", "parallelism": f"x-slab x{world}",
+                       "l2": "working set (10 volumes of %d MiB per GPU) exceeds the 126 MB L2" % (V >> 20),
+                       "e2e_def": "set_tilt_series(host) + K iterations (TV scalar read back each) + get_recon_all(host), K = steps"},
+            "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": int(S / args.steps),
+                    "d2h_bytes_per_step": int(V / args.steps) + 4},
+            "gpu_launches": launches,
+            "clocks": clk,
+            "roofline": roof,
+            "kernels": groups,
+            "iteration_roofline": iter_roof,
+        }
+    if rank == 0 and world == 1 and not args.no_cpu:
+        cores = os.cpu_count() or 1
+        nslab = max(1, min(cores, n))
+        sec, threads = cpu_fista_sample(n, na, nslab, 2, 1)
+        line["cpu_baseline"] = {"value": (1.0 / sec) * (nslab / n), "unit": UNIT, "cores": threads, "kind": "port",
+                                "sample": f"{nslab} of {n} slices per step (2 timed iterations), scaled by {n}/{nslab}"}
+    if rank == 0:
+        print(json.dumps(line), flush=True)
+    del eng
+    if dist is not None:
+        dist.destroy_process_group()
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=20)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--size", type=int, default=512)
+    ap.add_argument("--angles", type=int, default=180)
+    ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
+    args = ap.parse_args()
+    if args.impl == "reference":
+        run_reference(args)
+    else:
+        run_ours(args)
+
+
+if __name__ == "__main__":
+    main()

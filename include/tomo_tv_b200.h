@@ -25,6 +25,9 @@
 #ifdef __cplusplus
 extern "C" {
 #endif
+#if defined(__GNUC__)
+#pragma GCC visibility push(default)   /* the library is built with -fvisibility=hidden */
+#endif
 
 typedef struct ttv_engine* ttv_handle;
 
@@ -111,11 +114,22 @@ int ttv_set_model_projections(ttv_handle h, const float* g, int rows, int cols);
  * stream; *ms = average per launch.  names: fp, bp, sirt, fgp_sweep, fgp_first, fgp_final, fgp,
  * tv, momentum, tvgd_grad, tvgd_update, sqdist, fista_iter, kl, sart. */
 int ttv_time_kernel(ttv_handle h, const char* name, int reps, int arg_i, float arg_f, float* ms);
+/* per-kernel-group CUDA-event timing on the engine's stream: enable (resets the counters), run, then
+ * read total milliseconds and launch count per group.  groups: fp, bp, fgp_first, fgp_sweep, fgp_final,
+ * tv, momentum, tvgd_grad, tvgd_update, reduce, elementwise, sart_fp, sart_bp, io, halo. */
+int ttv_profile(ttv_handle h, int enable);
+int ttv_profile_get(ttv_handle h, const char* group, double* total_ms, long long* count);
+/* CUDA events on the engine's stream around an arbitrary sequence of calls */
+int ttv_timer_start(ttv_handle h);
+int ttv_timer_stop(ttv_handle h, float* ms);
 /* number of kernel launches issued by this engine so far */
 int ttv_launch_count(ttv_handle h, long long* n);
 /* algorithmic geometry facts for the roofline: bytes of one volume (V) and one sinogram (S) */
 int ttv_sizes(ttv_handle h, long long* V, long long* S, long long* samples_per_projection);
 
+#if defined(__GNUC__)
+#pragma GCC visibility pop
+#endif
 #ifdef __cplusplus
 }
 #endif

@@ -1,0 +1,65 @@
+import os
+import sys
+
+import numpy as np
+import pytest
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+for p in (ROOT, os.path.dirname(os.path.abspath(__file__))):
+    if p not in sys.path:
+        sys.path.insert(0, p)
+
+GOLDEN = os.path.join(ROOT, "tests", "golden")
+
+
+def pytest_configure(config):
+    config.addinivalue_line("markers", "gpu: needs a CUDA device (run on the B200 box)")
+
+
+def pytest_collection_modifyitems(config, items):
+    # GPU tests never run silently on a CPU fallback: without a device they are skipped here,
+    # and on a GPU box a missing CUDA library is a hard failure (see cuda_lib fixture).
+    try:
+        import torch
+        has_gpu = torch.cuda.is_available()
+    except Exception:
+        has_gpu = False
+    if has_gpu:
+        return
+    skip = pytest.mark.skip(reason="no CUDA device")
+    for it in items:
+        if "gpu" in it.keywords:
+            it.add_marker(skip)
+
+
+@pytest.fixture(scope="session")
+def orc():
+    import oracle
+    oracle.build()
+    return oracle
+
+
+@pytest.fixture(scope="session")
+def ttv():
+    """The product package with its CUDA library loaded; fails loudly if it is missing."""
+    import tomo_tv_b200
+    from tomo_tv_b200 import _native
+    _native.lib()
+    return tomo_tv_b200
+
+
+def golden_cases():
+    if not os.path.isdir(GOLDEN):
+        return []
+    out = []
+    for f in sorted(os.listdir(GOLDEN)):
+        if f.endswith(".npz") and not f.endswith("_inputs.npz"):
+            geom, scn = f[:-4].split("_", 1)
+            out.append((geom, scn))
+    return out
+
+
+def load_golden(geom, scn):
+    inp = dict(np.load(os.path.join(GOLDEN, f"{geom}_inputs.npz")))
+    want = dict(np.load(os.path.join(GOLDEN, f"{geom}_{scn}.npz")))
+    return inp, want

@@ -1,0 +1,225 @@
+"""Call sequences shared by the golden-vector generator (oracle/make_golden.py, run against the REAL
+reference extension on a B200) and the parity tests (run against the CPU oracle and the CUDA
+engine).  Every scenario only uses methods the reference binds on `tomoengine`
+(/root/reference/tomofusion/gpu/utils/tomoengine.cpp:487-534), so the same function drives all
+three implementations.
+"""
+import numpy as np
+
+GEOMS = {
+    # name: (Nslice, Nray, angles_deg)
+    "A": (34, 32, np.linspace(-90.0, 90.0, 12, endpoint=False)),
+    "B": (3, 80, np.concatenate([np.arange(-70.0, 72.0, 5.0), [-90.0, -45.0, 0.0, 45.0, 89.5]])),
+}
+
+
+def angles_rad(geom):
+    return np.deg2rad(GEOMS[geom][2]).astype(np.float32)
+
+
+def make_inputs(geom):
+    """Seeded inputs: a phantom volume, a noisy copy, and a generic positive sinogram."""
+    from tomo_tv_b200.phantom import phantom3d
+    nx, n, ang = GEOMS[geom]
+    rng = np.random.default_rng(7 + len(geom) + nx)
+    vol = phantom3d(nx, n, seed=11, nspheres=12)
+    noisy = (vol + 0.05 * rng.standard_normal(vol.shape)).astype(np.float32)
+    sino = rng.uniform(0.0, 1.0, (nx, len(ang) * n)).astype(np.float32)
+    return {"vol": vol, "noisy": noisy, "sino": sino}
+
+
+def volume(eng, nx):
+    return np.stack([np.asarray(eng.get_recon(s), dtype=np.float32) for s in range(nx)])
+
+
+def load_volume(eng, vol):
+    for s in range(vol.shape[0]):
+        eng.set_recon(np.ascontiguousarray(vol[s], dtype=np.float32), s)
+
+
+def sc_fp(eng, inp, nx):
+    """forward projection of a known volume (tomoengine.cpp:416-427)."""
+    eng.restart_recon()
+    eng.initialize_FP()
+    load_volume(eng, inp["vol"])
+    eng.forward_projection()
+    return {"g": np.asarray(eng.get_model_projections(), np.float32)}
+
+
+def sc_sirt(eng, inp, nx):
+    """SIRT from zero: iteration 1 pins R, C and the back projector; iteration 5 the loop."""
+    eng.set_tilt_series(inp["b"])
+    eng.initialize_SIRT()
+    eng.initialize_FP()
+    eng.restart_recon()
+    eng.SIRT(1)
+    r1 = volume(eng, nx)
+    eng.SIRT(4)
+    r5 = volume(eng, nx)
+    return {"recon1": r1, "recon5": r5, "dd": np.float32(eng.data_distance())}
+
+
+def sc_sart(eng, inp, nx):
+    eng.set_tilt_series(inp["b"])
+    eng.initialize_SART("sequential")
+    eng.initialize_FP()
+    eng.restart_recon()
+    eng.SART(1.0, 1)
+    r1 = volume(eng, nx)
+    eng.SART(0.5, 1)
+    r2 = volume(eng, nx)
+    return {"recon1": r1, "recon2": r2}
+
+
+def sc_kl(eng, inp, nx):
+    eng.set_tilt_series(inp["b"])
+    eng.restart_recon()
+    eng.initialize_poisson_ML()
+    eng.initialize_FP()
+    costs = [eng.poisson_ML(0.1) for _ in range(3)]
+    return {"recon": volume(eng, nx), "cost": np.asarray(costs, np.float32),
+            "bnorm": np.asarray(eng.get_projections(), np.float32)}
+
+
+def sc_kl_bp(eng, inp, nx):
+    """One KL step from a known volume against a generic sinogram: exercises the back projector
+    on an arbitrary (signed) sinogram (tomoengine.cpp:293-315)."""
+    eng.set_tilt_series(inp["sino"])
+    eng.restart_recon()
+    eng.initialize_poisson_ML()
+    eng.initialize_FP()
+    load_volume(eng, inp["vol"])
+    c = eng.poisson_ML(1.0)
+    return {"recon": volume(eng, nx), "cost": np.float32(c)}
+
+
+def sc_tv(eng, inp, nx):
+    eng.restart_recon()
+    load_volume(eng, inp["noisy"])
+    out = {"tv": np.float32(eng.tv())}
+    out["fgp_ret"] = np.float32(eng.tv_fgp(10, 0.1))
+    out["fgp"] = volume(eng, nx)
+    load_volume(eng, inp["noisy"])
+    out["fgp1_ret"] = np.float32(eng.tv_fgp(1, 0.1))
+    out["fgp1"] = volume(eng, nx)
+    load_volume(eng, inp["noisy"])
+    out["gd_ret"] = np.float32(eng.tv_gd(5, 0.5))
+    out["gd"] = volume(eng, nx)
+    load_volume(eng, inp["noisy"])
+    eng.tv_fgp(0, 0.1)
+    out["tvmap"] = volume(eng, nx)
+    return out
+
+
+def sc_fista(eng, inp, nx, niter=5, lam=0.1, ntv=10):
+    """The reference's FISTA loop (tomofusion/gpu/reconstructor.py:121-155), show_convergence on."""
+    eng.set_tilt_series(inp["b"])
+    eng.restart_recon()
+    eng.initialize_fista()
+    eng.initialize_FP()
+    eng.restart_recon()
+    cost = np.zeros(niter, np.float64)
+    t0 = 1.0
+    for k in range(niter):
+        eng.SIRT(1)
+        eng.tv_fgp(ntv, lam)
+        tk = 0.5 * (1 + np.sqrt(1 + 4 * t0 ** 2))
+        eng.fista_momentum((t0 - 1) / tk)
+        t0 = tk
+        cost[k] = 0.5 * eng.data_distance() ** 2 + lam * eng.tv()
+    return {"recon": volume(eng, nx), "cost": cost.astype(np.float32), "L": np.float32(eng.get_lipschitz())}
+
+
+def sc_fista_nomom(eng, inp, nx, niter=3, lam=0.1, ntv=5):
+    eng.set_tilt_series(inp["b"])
+    eng.restart_recon()
+    eng.initialize_fista()
+    eng.initialize_FP()
+    eng.restart_recon()
+    eng.remove_momentum()
+    for k in range(niter):
+        eng.SIRT(1)
+        eng.tv_fgp(ntv, lam)
+    return {"recon": volume(eng, nx)}
+
+
+def sc_asd(eng, inp, nx, niter=3, ng=5):
+    """Canonical ASD-POCS loop, tomofusion/examples/sim_ASD.py:66-94."""
+    eng.set_tilt_series(inp["b"])
+    eng.initialize_SART("sequential")
+    eng.initialize_FP()
+    eng.initialize_recon_copy()
+    eng.restart_recon()
+    beta, beta_red, alpha, alpha_red, r_max, eps = 0.25, 0.9985, 0.2, 0.95, 0.95, 0.025
+    dd, tv, dps = [], [], []
+    dPOCS = 0.0
+    for i in range(niter):
+        eng.copy_recon()
+        eng.SART(beta, 1)
+        beta *= beta_red
+        dp = eng.matrix_2norm()
+        if i == 0:
+            dPOCS = dp * alpha
+        dd.append(eng.data_distance())
+        eng.copy_recon()
+        tv.append(eng.tv_gd(ng, dPOCS))
+        dg = eng.matrix_2norm()
+        dps.append(dp)
+        if dg > dp * r_max and dd[-1] > eps:
+            dPOCS *= alpha_red
+    return {"recon": volume(eng, nx), "dd": np.asarray(dd, np.float32), "tv": np.asarray(tv, np.float32),
+            "dp": np.asarray(dps, np.float32)}
+
+
+def sc_misc(eng, inp, nx):
+    eng.restart_recon()
+    eng.initialize_initial_volume()
+    eng.initialize_recon_copy()
+    for s in range(nx):
+        eng.set_original_volume(np.ascontiguousarray(inp["vol"][s]), s)
+    load_volume(eng, inp["noisy"])
+    out = {"rmse": np.float32(eng.rmse()), "l1": np.float32(eng.l1_norm()),
+           "otv": np.float32(eng.original_tv())}
+    eng.copy_recon()
+    eng.soft_threshold(0.07)
+    out["soft"] = volume(eng, nx)
+    out["norm2"] = np.float32(eng.matrix_2norm())
+    eng.create_projections()
+    out["b"] = np.asarray(eng.get_projections(), np.float32)
+    return out
+
+
+SCENARIOS = {
+    "fp": sc_fp, "sirt": sc_sirt, "sart": sc_sart, "kl": sc_kl, "kl_bp": sc_kl_bp, "tv": sc_tv,
+    "fista": sc_fista, "fista_nomom": sc_fista_nomom, "asd": sc_asd, "misc": sc_misc,
+}
+
+# tolerances (relative L2 for arrays, relative for scalars), from BASELINE.json north_star:
+# projection operators 1e-5, reconstructions after a fixed iteration count 1e-4.
+TOL = {
+    ("fp", "g"): 1e-5, ("misc", "b"): 1e-5,
+    ("sirt", "recon1"): 1e-5,          # = C * BP(R * b): one application of the back projector
+    ("kl_bp", "recon"): 1e-5,
+}
+DEFAULT_TOL = 1e-4
+
+
+def rel_l2(a, b):
+    a = np.asarray(a, np.float64)
+    b = np.asarray(b, np.float64)
+    d = np.linalg.norm((a - b).ravel())
+    n = np.linalg.norm(b.ravel())
+    return d / n if n > 0 else d
+
+
+def compare(scn, got, want):
+    """-> list of (key, error, tolerance, ok)."""
+    rows = []
+    for k in sorted(want):
+        if k not in got:
+            rows.append((k, float("nan"), 0.0, False))
+            continue
+        tol = TOL.get((scn, k), DEFAULT_TOL)
+        e = rel_l2(got[k], want[k])
+        rows.append((k, float(e), tol, bool(e <= tol)))
+    return rows

@@ -1,0 +1,71 @@
+"""Host-side logic that needs no GPU: algorithm dispatch, tilt-series packing, slab partitioning."""
+import numpy as np
+import pytest
+
+
+class Spy:
+    def __init__(self):
+        self.calls = []
+
+    def __getattr__(self, name):
+        def f(*a):
+            self.calls.append((name,) + a)
+            return 1.25
+        return f
+
+
+def test_dispatch_matches_reference_table(ttv):
+    """tomofusion/pytvlib.py:5-31 -- note 'fista' runs one SIRT iteration."""
+    P = ttv.pytvlib
+    cases = {
+        "SIRT": ["initialize_SIRT"], "fista": ["initialize_fista"], "kl-divergence": ["initialize_poisson_ML"],
+        "CGLS": ["initialize_CGLS"],
+    }
+    for alg, first in cases.items():
+        s = Spy(); P.initialize_algorithm(s, alg)
+        assert [c[0] for c in s.calls] == first + ["initialize_FP"]
+    s = Spy(); P.initialize_algorithm(s, "SART", "random")
+    assert s.calls == [("initialize_SART", "random"), ("initialize_FP",)]
+    s = Spy(); P.initialize_algorithm(s, "asd-pocs", "sequential")
+    assert s.calls[0] == ("initialize_SART", "sequential")
+    s = Spy(); P.initialize_algorithm(s, "FBP", "hamming")
+    assert s.calls[0] == ("initialize_FBP", "hamming")
+    s = Spy(); P.run(s, "fista"); assert s.calls == [("SIRT", 1)]
+    s = Spy(); P.run(s, "SIRT"); assert s.calls == [("SIRT", 1)]
+    s = Spy(); P.run(s, "sart", 0.3); assert s.calls == [("SART", 0.3, 1)]
+    s = Spy(); assert P.run(s, "kl-divergence", 0.2) == 1.25 and s.calls == [("poisson_ML", 0.2)]
+    s = Spy(); P.run(s, "FBP"); assert s.calls == [("FBP", True)]
+    s = Spy(); P.run(s, "CGLS"); assert s.calls == [("CGLS", 1)]
+    assert len(P.wbp_filters()) == 12 and P.sart_orders() == ["sequential", "random"]
+
+
+def test_pack_tilt_series_matches_reference_loop(ttv):
+    from tomo_tv_b200.reconstructor import pack_tilt_series
+    rng = np.random.default_rng(0)
+    ts = rng.random((5, 7, 3))
+    b = np.zeros((5, 7 * 3))
+    for s in range(5):                       # the reference's per-slice loop, reconstructor.py:54-56
+        b[s, :] = ts[s, :, :].transpose().ravel()
+    got = pack_tilt_series(ts)
+    assert got.dtype == np.float32 and np.allclose(got, b.astype(np.float32))
+    with pytest.raises(ValueError):
+        pack_tilt_series(np.zeros((3, 3)))
+
+
+def test_slab_bounds_cover_the_volume(ttv):
+    from tomo_tv_b200.phantom import slab_bounds
+    for nslice in (1, 7, 8, 100, 512, 2048):
+        for nr in (1, 2, 3, 4, 8):
+            spans = [slab_bounds(nslice, nr, r) for r in range(nr)]
+            assert spans[0][0] == 0 and sum(c for _, c in spans) == nslice
+            for (f0, c0), (f1, _) in zip(spans, spans[1:]):
+                assert f0 + c0 == f1
+            assert max(c for _, c in spans) - min(c for _, c in spans) <= 1
+
+
+def test_phantom_is_deterministic(ttv):
+    from tomo_tv_b200.phantom import phantom3d
+    a = phantom3d(6, 32); b = phantom3d(6, 32)
+    assert a.dtype == np.float32 and a.shape == (6, 32, 32) and np.array_equal(a, b)
+    assert a.min() >= 0 and 0.2 < float(a.max()) <= 1.0
+    assert np.array_equal(phantom3d(6, 32, x0=2, count=3), a[2:5])

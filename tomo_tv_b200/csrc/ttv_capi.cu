@@ -195,8 +195,11 @@ int ttv_fista_momentum(ttv_handle h, float beta) {
     Engine& e = E(h);
     if (!e.yk.ok()) throw CudaError("fista_momentum called before initialize_fista");
     const size_t n4 = e.vol_elems() / 4;
-    momentum_kernel<<<ew_blocks(n4), 256, 0, e.st>>>(reinterpret_cast<float4*>(e.recon.p), reinterpret_cast<float4*>(e.yk.p),
-                                                      reinterpret_cast<float4*>(e.recon_old.p), beta, n4);
+    {
+        Engine::ProfScope ps(e, PF_MOMENTUM);
+        momentum_kernel<<<ew_blocks(n4), 256, 0, e.st>>>(reinterpret_cast<float4*>(e.recon.p), reinterpret_cast<float4*>(e.yk.p),
+                                                          reinterpret_cast<float4*>(e.recon_old.p), beta, n4);
+    }
     ++e.launches; TTV_LAUNCH_CHECK();
     e.sync();
     TTV_CATCH
@@ -296,6 +299,18 @@ int ttv_get_sirt_weights(ttv_handle h, float* R, float* C) {
     e.sync();
     TTV_CATCH
 }
+int ttv_profile(ttv_handle h, int enable) { TTV_TRY E(h).prof_enable(enable != 0); TTV_CATCH }
+int ttv_profile_get(ttv_handle h, const char* name, double* total_ms, long long* count) {
+    TTV_TRY
+    Engine& e = E(h);
+    e.prof_resolve();
+    for (int i = 0; i < PF_COUNT; ++i)
+        if (std::string(prof_name(i)) == name) { *total_ms = e.prof_ms[i]; *count = e.prof_n[i]; return 0; }
+    throw CudaError(std::string("ttv_profile_get: unknown kernel group '") + name + "'");
+    TTV_CATCH
+}
+int ttv_timer_start(ttv_handle h) { TTV_TRY E(h).timer_start(); TTV_CATCH }
+int ttv_timer_stop(ttv_handle h, float* ms) { TTV_TRY *ms = E(h).timer_stop(); TTV_CATCH }
 int ttv_launch_count(ttv_handle h, long long* n) { TTV_TRY *n = E(h).launches; TTV_CATCH }
 int ttv_sizes(ttv_handle h, long long* V, long long* S, long long* samples) {
     TTV_TRY

@@ -96,8 +96,61 @@ struct DBuf {
     bool ok() const { return p != nullptr; }
 };
 
+// Per-kernel-group timing with CUDA events on the engine's stream (bench.py's roofline numbers are
+// measured live inside the timed region, not under a profiler).
+enum ProfId { PF_FP = 0, PF_BP, PF_FGP_FIRST, PF_FGP_SWEEP, PF_FGP_FINAL, PF_TV, PF_MOMENTUM, PF_TVGD_GRAD, PF_TVGD_UPD,
+              PF_REDUCE, PF_EW, PF_SART_FP, PF_SART_BP, PF_IO, PF_HALO, PF_COUNT };
+inline const char* prof_name(int i) {
+    static const char* nm[PF_COUNT] = {"fp", "bp", "fgp_first", "fgp_sweep", "fgp_final", "tv", "momentum", "tvgd_grad", "tvgd_update",
+                                       "reduce", "elementwise", "sart_fp", "sart_bp", "io", "halo"};
+    return nm[i];
+}
+
 class Engine {
 public:
+    struct ProfRec { int id; cudaEvent_t a, b; };
+    bool prof_on = false;
+    std::vector<ProfRec> prof_pending;
+    double prof_ms[PF_COUNT] = {0};
+    long long prof_n[PF_COUNT] = {0};
+    struct ProfScope {
+        Engine& e; cudaEvent_t b = nullptr;
+        ProfScope(Engine& en, int id) : e(en) {
+            if (!e.prof_on) return;
+            cudaEvent_t a;
+            TTV_CUDA(cudaEventCreate(&a)); TTV_CUDA(cudaEventCreate(&b));
+            TTV_CUDA(cudaEventRecord(a, e.st));
+            e.prof_pending.push_back(ProfRec{id, a, b});
+        }
+        ~ProfScope() { if (b) cudaEventRecord(b, e.st); }
+    };
+    void prof_enable(bool on) {
+        prof_resolve();
+        prof_on = on;
+        if (on) for (int i = 0; i < PF_COUNT; ++i) { prof_ms[i] = 0; prof_n[i] = 0; }
+    }
+    void prof_resolve() {
+        if (prof_pending.empty()) return;
+        TTV_CUDA(cudaStreamSynchronize(st));
+        for (auto& r : prof_pending) {
+            float t = 0; cudaEventElapsedTime(&t, r.a, r.b);
+            prof_ms[r.id] += t; prof_n[r.id] += 1;
+            cudaEventDestroy(r.a); cudaEventDestroy(r.b);
+        }
+        prof_pending.clear();
+    }
+    cudaEvent_t tm_a = nullptr, tm_b = nullptr;
+    void timer_start() {
+        if (!tm_a) { TTV_CUDA(cudaEventCreate(&tm_a)); TTV_CUDA(cudaEventCreate(&tm_b)); }
+        TTV_CUDA(cudaEventRecord(tm_a, st));
+    }
+    float timer_stop() {
+        if (!tm_a) throw CudaError("timer_stop without timer_start");
+        TTV_CUDA(cudaEventRecord(tm_b, st)); TTV_CUDA(cudaEventSynchronize(tm_b));
+        float t = 0; TTV_CUDA(cudaEventElapsedTime(&t, tm_a, tm_b));
+        return t;
+    }
+
     int nx, N, Na = 0, nxb;          // local slices, Nray=Ny=Nz, angles, x-blocks
     int xoff, nxg;                   // slab position in the global volume
     int device, gpuID = -1;
@@ -154,6 +207,8 @@ public:
         for (DBuf* d : {&recon, &yk, &recon_old, &temp, &original, &b, &g, &r, &scratch, &R, &C, &stage, &planes}) d->release();
         for (auto& d : P) d.release();
         cudaFree(d_win0); cudaFree(d_fpang); cudaFree(d_fpgrp); cudaFree(d_theta); cudaFree(d_red); cudaFree(d_imax);
+        for (auto& r : prof_pending) { cudaEventDestroy(r.a); cudaEventDestroy(r.b); }
+        if (tm_a) { cudaEventDestroy(tm_a); cudaEventDestroy(tm_b); }
         if (st) cudaStreamDestroy(st);
     }
 
@@ -311,6 +366,7 @@ public:
         p.N = N; p.Nd = N; p.Na = Na; p.ndg = fp_ndg; p.CW = fp_CW; p.TR = fp_TR; p.S = fp_S;
         p.out = out; p.b = bmeas; p.R = R.p; p.red = red; p.eps = eps;
         dim3 grid(fp_ndg, fp_ngroups, zb);
+        ProfScope ps(*this, PF_FP);
         fp_kernel<EPI><<<grid, FP_THREADS, fp_smem, st>>>(tmV, tmH, p);
         TTV_LAUNCH_CHECK(); ++launches;
     }
@@ -322,6 +378,7 @@ public:
         BpParams p; p.N = N; p.Nd = N; p.Na = Na; p.vol = vol; p.C = C.p; p.step = step;
         const int nt = (N + BP_TILE - 1) / BP_TILE;
         dim3 grid(nt, nt, zb);
+        ProfScope ps(*this, PF_BP);
         bp_kernel<EPI><<<grid, BP_THREADS, BP_SMEM, st>>>(tmS, p);
         TTV_LAUNCH_CHECK(); ++launches;
     }
@@ -438,6 +495,7 @@ public:
     void exchange(const float* src, int xs, int to, float* sendbuf, int from, float* recvbuf) {
         Nccl& n = Nccl::get();
         const int64_t M = (int64_t)N * N;
+        ProfScope ps(*this, PF_HALO);
         if (to >= 0) { gather_slice_kernel<<<256, 256, 0, st>>>(src, sendbuf, xs, M); ++launches; }
         n.check(n.GroupStart(), "ncclGroupStart");
         if (to >= 0) n.check(n.Send(sendbuf, M, Nccl::Float32, to, comm, st), "ncclSend");
@@ -456,7 +514,10 @@ public:
         }
         zero_red(0);
         const int64_t rows = (int64_t)nxb * N;
-        tv_value_kernel<<<(unsigned)((rows + 7) / 8), 256, 0, st>>>(v, dims(), hn, d_red); ++launches;
+        {
+            ProfScope ps(*this, PF_TV);
+            tv_value_kernel<<<(unsigned)((rows + 7) / 8), 256, 0, st>>>(v, dims(), hn, d_red); ++launches;
+        }
         TTV_LAUNCH_CHECK();
         return read_red(0);
     }
@@ -504,10 +565,12 @@ public:
             } else { p.P1 = p.P2 = p.P3 = nullptr; }
             if (last) {
                 dim3 g2((N + TV_KSEG - 1) / TV_KSEG, (N + 7) / 8, nxb);
+                ProfScope ps(*this, PF_FGP_FINAL);
                 fgp_final_kernel<<<g2, 256, 0, st>>>(p, scratch.p); ++launches;
             } else {
                 const int nxt = first ? 0 : 1 - cur;
                 p.Q1 = P[nxt * 3 + 0].p; p.Q2 = P[nxt * 3 + 1].p; p.Q3 = P[nxt * 3 + 2].p;
+                ProfScope ps(*this, first ? PF_FGP_FIRST : PF_FGP_SWEEP);
                 if (first) fgp_sweep_kernel<true><<<grid, TV_WARPS * 32, 0, st>>>(p);
                 else fgp_sweep_kernel<false><<<grid, TV_WARPS * 32, 0, st>>>(p);
                 ++launches;
@@ -535,13 +598,19 @@ public:
                 p.hm = plane(1); p.hp = plane(3);
             }
             zero_red(1);
-            tvgd_gradient_kernel<<<grid, 256, 0, st>>>(p); ++launches;
+            {
+                ProfScope ps(*this, PF_TVGD_GRAD);
+                tvgd_gradient_kernel<<<grid, 256, 0, st>>>(p); ++launches;
+            }
             TTV_LAUNCH_CHECK();
             if (nranks > 1) {
                 Nccl& nc = Nccl::get();
                 nc.check(nc.AllReduce(d_red + 1, d_red + 1, 1, Nccl::Float64, Nccl::Sum, comm, st), "ncclAllReduce");
             }
-            tvgd_update_kernel<<<ew_blocks(n / 4), 256, 0, st>>>(recon.p, scratch.p, d_red + 1, dPOCS, it == ng - 1 ? 1 : 0, n / 4); ++launches;
+            {
+                ProfScope ps(*this, PF_TVGD_UPD);
+                tvgd_update_kernel<<<ew_blocks(n / 4), 256, 0, st>>>(recon.p, scratch.p, d_red + 1, dPOCS, it == ng - 1 ? 1 : 0, n / 4); ++launches;
+            }
             TTV_LAUNCH_CHECK();
         }
         if (ng <= 0) { ew_kernel<EW_POS><<<ew_blocks(n / 4), 256, 0, st>>>(reinterpret_cast<float4*>(recon.p), 0.f, n / 4); ++launches; }
@@ -551,6 +620,7 @@ public:
 
     template <int OP> double reduce(const float* a, const float* bb, size_t n) {
         zero_red(2);
+        ProfScope ps(*this, PF_REDUCE);
         reduce_kernel<OP><<<ew_blocks(n / 4), 256, 0, st>>>(reinterpret_cast<const float4*>(a), reinterpret_cast<const float4*>(bb), n / 4, d_red + 2);
         ++launches; TTV_LAUNCH_CHECK();
         return read_red(2);

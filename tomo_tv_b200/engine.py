@@ -100,6 +100,14 @@ class tomoengine:
         check(lib().ttv_get_recon_all(self._h, _p(out)))
         return out
 
+    def get_recon_all_into(self, out):
+        """Bulk copy into a caller-provided C-contiguous float32 [Nslice, Nray, Nray] buffer
+        (e.g. pinned memory)."""
+        if out.dtype != np.float32 or not out.flags.c_contiguous or out.shape != (self.Nslice, self.Nray, self.Nray):
+            raise ValueError("get_recon_all_into expects a C-contiguous float32 [Nslice, Nray, Nray] array")
+        check(lib().ttv_get_recon_all(self._h, _p(out)))
+        return out
+
     def set_recon_all(self, vol):
         v = _as_f32(vol)
         if v.shape != (self.Nslice, self.Nray, self.Nray):
@@ -260,6 +268,30 @@ class tomoengine:
     def time_kernel(self, name, reps=10, arg_i=0, arg_f=0.0):
         v = C.c_float(0)
         check(lib().ttv_time_kernel(self._h, name.encode(), int(reps), int(arg_i), C.c_float(arg_f), C.byref(v)))
+        return v.value
+
+    PROFILE_GROUPS = ("fp", "bp", "fgp_first", "fgp_sweep", "fgp_final", "tv", "momentum", "tvgd_grad",
+                      "tvgd_update", "reduce", "elementwise", "sart_fp", "sart_bp", "io", "halo")
+
+    def profile(self, enable=True):
+        check(lib().ttv_profile(self._h, int(bool(enable))))
+
+    def profile_report(self):
+        """{group: (total_ms, launches)} measured with CUDA events on the engine's stream."""
+        out = {}
+        for g in self.PROFILE_GROUPS:
+            ms, n = C.c_double(0), C.c_longlong(0)
+            check(lib().ttv_profile_get(self._h, g.encode(), C.byref(ms), C.byref(n)))
+            if n.value:
+                out[g] = (ms.value, n.value)
+        return out
+
+    def timer_start(self):
+        check(lib().ttv_timer_start(self._h))
+
+    def timer_stop(self):
+        v = C.c_float(0)
+        check(lib().ttv_timer_stop(self._h, C.byref(v)))
         return v.value
 
     def launch_count(self):
