@@ -48,7 +48,14 @@ typedef struct {
 ORC_API void orc_geometry(int nang, int ndet, const float* angles, orc_angle_t* out)
 {
     for (int i = 0; i < nang; ++i) {
-        double al = (double)angles[i];
+        /* CProjectionGeometry2D::_check (A/src/ProjectionGeometry2D.cpp:98-102) wraps every angle
+         * into [0, 2pi) in float32 arithmetic with the float32 constant PI (A/include/astra/Globals.h:108);
+         * for negative tilt angles this perturbs the angle by ~2e-7 rad, which is visible at 1e-5. */
+        const float twopi = 2 * 3.14159265358979323846264338328f;
+        float af = angles[i];
+        while (twopi <= af) af -= twopi;
+        while (af < 0) af += twopi;
+        double al = (double)af;
         double c = cos(al), s = sin(al);
         float bDetSX = (float)(ndet * 1.0 * -0.5f);
         /* ROTATE0: X' = X cos - Y sin ; Y' = X sin + Y cos */

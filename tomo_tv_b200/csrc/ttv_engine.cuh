@@ -229,7 +229,13 @@ public:
         angles.assign(ang, ang + nang);
         geom.resize(Na);
         for (int i = 0; i < Na; ++i) {
-            const double al = (double)angles[i], c = std::cos(al), s = std::sin(al);
+            // the reference wraps angles into [0, 2pi) in float32 (A/src/ProjectionGeometry2D.cpp:98-102,
+            // float32 PI from A/include/astra/Globals.h:108); negative tilt angles move by ~2e-7 rad
+            const float twopi = 2 * 3.14159265358979323846264338328f;
+            float af = angles[i];
+            while (twopi <= af) af -= twopi;
+            while (af < 0) af += twopi;
+            const double al = (double)af, c = std::cos(al), s = std::sin(al);
             const float bDetSX = (float)(N * 1.0 * -0.5f);
             const float rayX = (float)(0.0 * c - 1.0 * s), rayY = (float)(0.0 * s + 1.0 * c);
             const float detSX = (float)((double)bDetSX * c), detSY = (float)((double)bDetSX * s);
@@ -262,7 +268,9 @@ public:
         weights_ready = false; sart_ready = false; kl_ready = false;
     }
 
-    // angles sorted by (orientation, theta), groups of <= ag, per-line staging windows
+    // Forward-projector plan: angles sorted by (orientation, theta) and packed greedily into groups
+    // of <= FP_AG angles whose rays stay close enough that one staged window per line (<= cw_limit
+    // cells) serves the whole group; per (group, detector group, line) the first staged cell.
     void build_fp_plan() {
         std::vector<int> vert, hori;
         for (int i = 0; i < Na; ++i) (geom[i].vertical ? vert : hori).push_back(i);
@@ -272,72 +280,82 @@ public:
         const int ndg = (N + FP_DG - 1) / FP_DG;
         const size_t budget = 200 * 1024;
         int TR = 2;
-        for (int ag = FP_AG; ag >= 1; ag /= 2) {
-            std::vector<FpAngle> fa; std::vector<FpGroup> fg;
-            for (int pass = 0; pass < 2; ++pass) {
-                const std::vector<int>& lst = pass == 0 ? vert : hori;
-                for (size_t i = 0; i < lst.size(); i += ag) {
-                    FpGroup G; G.first = (int)fa.size(); G.count = (int)std::min<size_t>(ag, lst.size() - i); G.vertical = pass == 0; G.pad = 0;
-                    for (int k = 0; k < G.count; ++k) {
-                        const AngleGeom& q = geom[lst[i + k]];
-                        fa.push_back(FpAngle{q.theta, q.detsize, q.offset, lst[i + k]});
-                    }
-                    fg.push_back(G);
+        const int nlines = ((N + TR - 1) / TR) * TR;
+        // sample position (cell coordinate) of detector d on line `line` for angle index ai
+        auto pos = [&](int ai, bool vertical, int d, int line) -> double {
+            const AngleGeom& q = geom[ai];
+            const double c = std::cos((double)q.theta), s = std::sin((double)q.theta);
+            double detStep, step;
+            if (vertical) { detStep = q.detsize / c; step = s / c; }
+            else { detStep = -q.detsize / s; step = c / s; }
+            return (d - 0.5 * N + 0.5 - q.offset) * detStep + (line - 0.5 * N + 0.5) * step + 0.5 * N;
+        };
+        auto window = [&](const int* members, int count, bool vertical, int dgi, int line, int& w0, int& wend) {
+            const int dlo = dgi * FP_DG, dhi = std::min(dlo + FP_DG - 1, N - 1);
+            double pmin = 1e30, pmax = -1e30;
+            for (int k = 0; k < count; ++k)
+                for (int d : {dlo, dhi}) {
+                    const double pp = pos(members[k], vertical, d, line);
+                    pmin = std::min(pmin, pp); pmax = std::max(pmax, pp);
                 }
-            }
-            const int nlines = ((N + TR - 1) / TR) * TR;
-            std::vector<int> win((size_t)fg.size() * ndg * nlines);
-            int CW = 0;
-            for (size_t gi = 0; gi < fg.size(); ++gi) {
-                for (int dgi = 0; dgi < ndg; ++dgi) {
-                    const int dlo = dgi * FP_DG, dhi = std::min(dlo + FP_DG - 1, N - 1);
-                    for (int line = 0; line < nlines; ++line) {
-                        double pmin = 1e30, pmax = -1e30;
-                        for (int k = 0; k < fg[gi].count; ++k) {
-                            const FpAngle& A = fa[fg[gi].first + k];
-                            const double c = std::cos((double)A.theta), s = std::sin((double)A.theta);
-                            double detStep, step;
-                            if (fg[gi].vertical) { detStep = A.detsize / c; step = s / c; }
-                            else { detStep = -A.detsize / s; step = c / s; }
-                            for (int d : {dlo, dhi}) {
-                                const double pp = (d - 0.5 * N + 0.5 - A.offset) * detStep + (line - 0.5 * N + 0.5) * step + 0.5 * N;
-                                pmin = std::min(pmin, pp); pmax = std::max(pmax, pp);
-                            }
-                        }
-                        const int w0 = (int)std::floor(pmin - 0.5) - 1;
-                        const int wend = (int)std::floor(pmax - 0.5) + 3;
-                        win[(gi * ndg + dgi) * nlines + line] = w0;
-                        CW = std::max(CW, wend - w0 + 1);
-                    }
+            w0 = (int)std::floor(pmin - 0.5) - 1;
+            wend = (int)std::floor(pmax - 0.5) + 3;
+        };
+        // widest window of a candidate group (positions are linear in the line index: check both ends)
+        auto group_cw = [&](const int* members, int count, bool vertical) {
+            int cw = 0;
+            for (int dgi = 0; dgi < ndg; ++dgi)
+                for (int line : {0, nlines - 1}) {
+                    int w0, wend; window(members, count, vertical, dgi, line, w0, wend);
+                    cw = std::max(cw, wend - w0 + 1);
                 }
+            return cw;
+        };
+        const int cw_limit = 160;
+        std::vector<FpAngle> fa; std::vector<FpGroup> fg; std::vector<int> order;
+        for (int pass = 0; pass < 2; ++pass) {
+            const std::vector<int>& lst = pass == 0 ? vert : hori;
+            size_t i = 0;
+            while (i < lst.size()) {
+                int cnt = 1;
+                while (cnt < FP_AG && i + cnt < lst.size() && group_cw(&lst[i], cnt + 1, pass == 0) <= cw_limit) ++cnt;
+                FpGroup G; G.first = (int)fa.size(); G.count = cnt; G.vertical = pass == 0; G.pad = 0;
+                for (int k = 0; k < cnt; ++k) {
+                    const AngleGeom& q = geom[lst[i + k]];
+                    fa.push_back(FpAngle{q.theta, q.detsize, q.offset, lst[i + k]});
+                    order.push_back(lst[i + k]);
+                }
+                fg.push_back(G);
+                i += cnt;
             }
-            if (CW > 256 && ag > 1) continue;
-            if (CW > 256) throw CudaError("forward-projector window exceeds the TMA box limit");
-            size_t stage_b = (size_t)TR * CW * 128;
-            int S = (int)std::min<size_t>(FP_MAX_STAGES, budget / stage_b);
-            if (S < 2) { TR = 1; stage_b = (size_t)CW * 128; S = (int)std::min<size_t>(FP_MAX_STAGES, budget / stage_b); }
-            fp_CW = CW; fp_TR = TR; fp_S = S; fp_ngroups = (int)fg.size(); fp_ndg = ndg;
-            fp_smem = (size_t)S * stage_b + (size_t)(S * TR + 1) * sizeof(float) + 2 * S * sizeof(uint64_t) + 16;
-            if (TR == 1) {   // rebuild the table with nlines = N
-                std::vector<int> w1((size_t)fg.size() * ndg * N);
-                for (size_t q = 0; q < fg.size() * (size_t)ndg; ++q)
-                    for (int line = 0; line < N; ++line) w1[q * N + line] = win[q * nlines + line];
-                win.swap(w1);
-            }
-            cudaFree(d_win0); cudaFree(d_fpang); cudaFree(d_fpgrp); cudaFree(d_theta);
-            TTV_CUDA(cudaMalloc(&d_win0, win.size() * sizeof(int)));
-            TTV_CUDA(cudaMalloc(&d_fpang, fa.size() * sizeof(FpAngle)));
-            TTV_CUDA(cudaMalloc(&d_fpgrp, fg.size() * sizeof(FpGroup)));
-            TTV_CUDA(cudaMalloc(&d_theta, Na * sizeof(float)));
-            TTV_CUDA(cudaMemcpy(d_win0, win.data(), win.size() * sizeof(int), cudaMemcpyHostToDevice));
-            TTV_CUDA(cudaMemcpy(d_fpang, fa.data(), fa.size() * sizeof(FpAngle), cudaMemcpyHostToDevice));
-            TTV_CUDA(cudaMemcpy(d_fpgrp, fg.data(), fg.size() * sizeof(FpGroup), cudaMemcpyHostToDevice));
-            std::vector<float> th(Na);
-            for (int i = 0; i < Na; ++i) th[i] = geom[i].theta;
-            TTV_CUDA(cudaMemcpy(d_theta, th.data(), Na * sizeof(float), cudaMemcpyHostToDevice));
-            set_fp_attrs();
-            return;
         }
+        std::vector<int> win((size_t)fg.size() * ndg * nlines);
+        int CW = 0;
+        for (size_t gi = 0; gi < fg.size(); ++gi)
+            for (int dgi = 0; dgi < ndg; ++dgi)
+                for (int line = 0; line < nlines; ++line) {
+                    int w0, wend; window(&order[fg[gi].first], fg[gi].count, fg[gi].vertical != 0, dgi, line, w0, wend);
+                    win[(gi * ndg + dgi) * nlines + line] = w0;
+                    CW = std::max(CW, wend - w0 + 1);
+                }
+        if (CW > 256) throw CudaError("forward-projector window exceeds the TMA box limit");
+        size_t stage_b = (size_t)TR * CW * 128;
+        int S = (int)std::min<size_t>(FP_MAX_STAGES, budget / stage_b);
+        if (S < 2) throw CudaError("forward-projector stage does not fit in shared memory");
+        fp_CW = CW; fp_TR = TR; fp_S = S; fp_ngroups = (int)fg.size(); fp_ndg = ndg;
+        fp_smem = (size_t)S * stage_b + (size_t)(S * TR + 1) * sizeof(float) + 2 * S * sizeof(uint64_t) + 16;
+        cudaFree(d_win0); cudaFree(d_fpang); cudaFree(d_fpgrp); cudaFree(d_theta);
+        TTV_CUDA(cudaMalloc(&d_win0, win.size() * sizeof(int)));
+        TTV_CUDA(cudaMalloc(&d_fpang, fa.size() * sizeof(FpAngle)));
+        TTV_CUDA(cudaMalloc(&d_fpgrp, fg.size() * sizeof(FpGroup)));
+        TTV_CUDA(cudaMalloc(&d_theta, Na * sizeof(float)));
+        TTV_CUDA(cudaMemcpy(d_win0, win.data(), win.size() * sizeof(int), cudaMemcpyHostToDevice));
+        TTV_CUDA(cudaMemcpy(d_fpang, fa.data(), fa.size() * sizeof(FpAngle), cudaMemcpyHostToDevice));
+        TTV_CUDA(cudaMemcpy(d_fpgrp, fg.data(), fg.size() * sizeof(FpGroup), cudaMemcpyHostToDevice));
+        std::vector<float> th(Na);
+        for (int i = 0; i < Na; ++i) th[i] = geom[i].theta;
+        TTV_CUDA(cudaMemcpy(d_theta, th.data(), Na * sizeof(float), cudaMemcpyHostToDevice));
+        set_fp_attrs();
     }
     template <int EPI> void fp_attr() {
         TTV_CUDA(cudaFuncSetAttribute(fp_kernel<EPI>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)fp_smem));

@@ -134,6 +134,7 @@ fp_kernel(const __grid_constant__ CUtensorMap tmV, const __grid_constant__ CUten
     for (int it = 0; it < nstages_total; ++it) {
         const int s = it % S;
         mbar_wait(&full[s], (it / S) & 1);
+        if (angle_ok)                 // warp-uniform: warps of a partially filled group only keep the ring moving
         for (int l = 0; l < TR; ++l) {
             const int line = it * TR + l;
             const float Cl = s_C[s * TR + l];
