@@ -311,6 +311,14 @@ int ttv_profile_get(ttv_handle h, const char* name, double* total_ms, long long*
 }
 int ttv_timer_start(ttv_handle h) { TTV_TRY E(h).timer_start(); TTV_CATCH }
 int ttv_timer_stop(ttv_handle h, float* ms) { TTV_TRY *ms = E(h).timer_stop(); TTV_CATCH }
+int ttv_set_option(ttv_handle h, const char* name, int value) {
+    TTV_TRY
+    Engine& e = E(h);
+    const std::string nm = name ? name : "";
+    if (nm == "fgp_tiled") e.fgp_tiled = value != 0;
+    else throw CudaError("ttv_set_option: unknown option '" + nm + "'");
+    TTV_CATCH
+}
 int ttv_launch_count(ttv_handle h, long long* n) { TTV_TRY *n = E(h).launches; TTV_CATCH }
 int ttv_sizes(ttv_handle h, long long* V, long long* S, long long* samples) {
     TTV_TRY
@@ -343,9 +351,12 @@ int ttv_time_kernel(ttv_handle h, const char* name, int reps, int arg_i, float a
         else if (nm == "bp") e.bp<BP_STORE>(e.g.p, e.scratch.p);
         else if (nm == "bp_sirt") e.bp<BP_SIRT_UPD>(e.r.p, e.yk.p);
         else if (nm == "sirt") e.sirt_step(e.yk.p);
-        else if (nm == "fgp_sweep") { fgp_sweep_kernel<false><<<gsw, TV_WARPS * 32, 0, e.st>>>(fp); ++e.launches; }
-        else if (nm == "fgp_first") { fgp_sweep_kernel<true><<<gsw, TV_WARPS * 32, 0, e.st>>>(fp); ++e.launches; }
-        else if (nm == "fgp_final") { fgp_final_kernel<<<dim3(gsw.x, (e.N + 7) / 8, e.nxb), 256, 0, e.st>>>(fp, e.scratch.p); ++e.launches; }
+        else if (nm == "fgp_sweep_v1") { fgp_sweep_kernel<false><<<gsw, TV_WARPS * 32, 0, e.st>>>(fp); ++e.launches; }
+        else if (nm == "fgp_first_v1") { fgp_sweep_kernel<true><<<gsw, TV_WARPS * 32, 0, e.st>>>(fp); ++e.launches; }
+        else if (nm == "fgp_final_v1") { fgp_final_kernel<<<dim3(gsw.x, (e.N + 7) / 8, e.nxb), 256, 0, e.st>>>(fp, e.scratch.p); ++e.launches; }
+        else if (nm == "fgp_sweep") e.fgp_launch(FGP_SWEEP, fp, nullptr);
+        else if (nm == "fgp_first") e.fgp_launch(FGP_FIRST, fp, nullptr);
+        else if (nm == "fgp_final") e.fgp_launch(FGP_FINAL, fp, e.scratch.p);
         else if (nm == "tv") { tv_value_kernel<<<(unsigned)((rows + 7) / 8), 256, 0, e.st>>>(e.recon.p, e.dims(), nullptr, e.d_red); ++e.launches; }
         else if (nm == "momentum") { momentum_kernel<<<ew_blocks(n / 4), 256, 0, e.st>>>(reinterpret_cast<float4*>(e.scratch.p), reinterpret_cast<float4*>(e.yk.p), reinterpret_cast<float4*>(e.recon_old.p), 0.5f, n / 4); ++e.launches; }
         else if (nm == "tvgd_grad") { tvgd_gradient_kernel<<<dim3(gsw.x, (e.N + 7) / 8, e.nxb), 256, 0, e.st>>>(gp); ++e.launches; }

@@ -10,6 +10,7 @@
 #include "ttv_fp.cuh"
 #include "ttv_bp.cuh"
 #include "ttv_tv.cuh"
+#include "ttv_fgp.cuh"
 #include "ttv_elem.cuh"
 #include <vector>
 #include <string>
@@ -38,11 +39,11 @@ inline PFN_encodeTiled get_encode_tiled() {
     return fn;
 }
 // 4-D map over an x-interleaved array [d3][d2][d1][32] of float32 with the given box.
-inline CUtensorMap make_tmap(const float* base, uint64_t d1, uint64_t d2, uint64_t d3, uint32_t b1, uint32_t b2) {
+inline CUtensorMap make_tmap(const float* base, uint64_t d1, uint64_t d2, uint64_t d3, uint32_t b1, uint32_t b2, uint32_t b0 = 32) {
     CUtensorMap tm;
     cuuint64_t dims[4] = {32, d1, d2, d3};
     cuuint64_t strides[3] = {128, 128 * d1, 128 * d1 * d2};
-    cuuint32_t box[4] = {32, b1, b2, 1};
+    cuuint32_t box[4] = {b0, b1, b2, 1};
     cuuint32_t estr[4] = {1, 1, 1, 1};
     CUresult r = get_encode_tiled()(&tm, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 4, const_cast<float*>(base), dims, strides, box, estr,
                                     CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_NONE, CU_TENSOR_MAP_L2_PROMOTION_L2_128B,
@@ -199,6 +200,9 @@ public:
         TTV_CUDA(cudaMalloc(&d_imax, sizeof(int)));
         size_t stage_elems = (size_t)32 * std::max<size_t>((size_t)N * N, 1);
         stage.alloc(stage_elems);
+        TTV_CUDA(cudaFuncSetAttribute(fgp_tile_kernel<FGP_SWEEP>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)FGP_SMEM));
+        TTV_CUDA(cudaFuncSetAttribute(fgp_tile_kernel<FGP_FIRST>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)FGP_SMEM));
+        TTV_CUDA(cudaFuncSetAttribute(fgp_tile_kernel<FGP_FINAL>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)FGP_SMEM));
         if (nang > 0) set_angles(ang, nang);
     }
     ~Engine() {
@@ -540,6 +544,27 @@ public:
         return read_red(0);
     }
 
+    // one tiled FGP launch (ttv_fgp.cuh); mode FGP_FIRST ignores P, FGP_FINAL writes D to `out`
+    bool fgp_tiled = true;
+    int fgp_seg() const { return N >= 64 ? 64 : ((N + 1) & ~1); }
+    void fgp_launch(int mode, const FgpParams& p, float* out) {
+        FgpMaps tm;
+        tm.in = make_tmap(p.in, N, N, nxb, FGP_CW, FGP_RJ);
+        tm.inh = make_tmap(p.in, N, N, nxb, FGP_CW, FGP_RJ, 4);
+        if (mode == FGP_FIRST) { tm.p1 = tm.p2 = tm.p3 = tm.in; tm.p1h = tm.p2h = tm.p3h = tm.inh; }
+        else {
+            tm.p1 = make_tmap(p.P1, N, N, nxb, FGP_CW, FGP_RJ); tm.p1h = make_tmap(p.P1, N, N, nxb, FGP_CW, FGP_RJ, 4);
+            tm.p2 = make_tmap(p.P2, N, N, nxb, FGP_CW, FGP_RJ); tm.p2h = make_tmap(p.P2, N, N, nxb, FGP_CW, FGP_RJ, 4);
+            tm.p3 = make_tmap(p.P3, N, N, nxb, FGP_CW, FGP_RJ); tm.p3h = make_tmap(p.P3, N, N, nxb, FGP_CW, FGP_RJ, 4);
+        }
+        const int seg = fgp_seg();
+        dim3 grid(nxb, (N + FGP_TK - 1) / FGP_TK, (N + seg - 1) / seg);
+        if (mode == FGP_FIRST) fgp_tile_kernel<FGP_FIRST><<<grid, FGP_THREADS, FGP_SMEM, st>>>(tm, p, out, seg);
+        else if (mode == FGP_FINAL) fgp_tile_kernel<FGP_FINAL><<<grid, FGP_THREADS, FGP_SMEM, st>>>(tm, p, out, seg);
+        else fgp_tile_kernel<FGP_SWEEP><<<grid, FGP_THREADS, FGP_SMEM, st>>>(tm, p, out, seg);
+        ++launches;
+    }
+
     // cuda_tv_fgp_3D, tv_fgp.cu:192-281.  Returns TV of the input.
     float tv_fgp(int iter, float lambda) {
         use();
@@ -584,14 +609,18 @@ public:
             if (last) {
                 dim3 g2((N + TV_KSEG - 1) / TV_KSEG, (N + 7) / 8, nxb);
                 ProfScope ps(*this, PF_FGP_FINAL);
-                fgp_final_kernel<<<g2, 256, 0, st>>>(p, scratch.p); ++launches;
+                if (fgp_tiled && !first) fgp_launch(FGP_FINAL, p, scratch.p);
+                else { fgp_final_kernel<<<g2, 256, 0, st>>>(p, scratch.p); ++launches; }
             } else {
                 const int nxt = first ? 0 : 1 - cur;
                 p.Q1 = P[nxt * 3 + 0].p; p.Q2 = P[nxt * 3 + 1].p; p.Q3 = P[nxt * 3 + 2].p;
                 ProfScope ps(*this, first ? PF_FGP_FIRST : PF_FGP_SWEEP);
-                if (first) fgp_sweep_kernel<true><<<grid, TV_WARPS * 32, 0, st>>>(p);
-                else fgp_sweep_kernel<false><<<grid, TV_WARPS * 32, 0, st>>>(p);
-                ++launches;
+                if (fgp_tiled) fgp_launch(first ? FGP_FIRST : FGP_SWEEP, p, nullptr);
+                else {
+                    if (first) fgp_sweep_kernel<true><<<grid, TV_WARPS * 32, 0, st>>>(p);
+                    else fgp_sweep_kernel<false><<<grid, TV_WARPS * 32, 0, st>>>(p);
+                    ++launches;
+                }
                 cur = nxt;
             }
             TTV_LAUNCH_CHECK();

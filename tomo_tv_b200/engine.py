@@ -246,6 +246,9 @@ class tomoengine:
     def sync(self):
         check(lib().ttv_sync(self._h))
 
+    def set_option(self, name, value):
+        check(lib().ttv_set_option(self._h, str(name).encode(), int(value)))
+
     def get_trig(self):
         c = np.empty(self.Nproj, np.float32)
         s = np.empty(self.Nproj, np.float32)
