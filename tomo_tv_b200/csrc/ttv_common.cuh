@@ -96,6 +96,10 @@ __device__ __forceinline__ float lds32(uint32_t addr) {
     return v;
 }
 
+__device__ __forceinline__ void sts32(uint32_t addr, float v) {
+    asm volatile("st.shared.f32 [%0], %1;" ::"r"(addr), "f"(v) : "memory");
+}
+
 // Texture-unit interpolation model (cudaFilterModeLinear, A/cuda/2d/util.cu:161-179,198-223):
 // the coordinate is converted to fixed point with 8 fractional bits (round to nearest), 0.5 is
 // subtracted, the integer part selects the texel pair and the 8-bit fraction is the weight.
