@@ -134,7 +134,7 @@ int ttv_SIRT(ttv_handle h, int niter) {
     if (!e.weights_ready) throw CudaError("SIRT called before initialize_SIRT");
     float* tgt = e.momentum ? e.yk.p : e.recon.p;           // tomoengine.cpp:194-195
     for (int i = 0; i < niter; ++i) e.sirt_step(tgt);
-    e.sync();
+    /* stream-ordered: void methods do not block the host (every getter / scalar method synchronises) */
     TTV_CATCH
 }
 int ttv_initialize_SART(ttv_handle h, const char* order) {
@@ -201,7 +201,6 @@ int ttv_fista_momentum(ttv_handle h, float beta) {
                                                           reinterpret_cast<float4*>(e.recon_old.p), beta, n4);
     }
     ++e.launches; TTV_LAUNCH_CHECK();
-    e.sync();
     TTV_CATCH
 }
 
@@ -226,7 +225,6 @@ int ttv_copy_recon(ttv_handle h) {
     Engine& e = E(h);
     if (!e.temp.ok()) throw CudaError("copy_recon called before initialize_recon_copy");
     TTV_CUDA(cudaMemcpyAsync(e.temp.p, e.recon.p, e.vol_elems() * sizeof(float), cudaMemcpyDeviceToDevice, e.st));
-    e.sync();
     TTV_CATCH
 }
 int ttv_matrix_2norm(ttv_handle h, float* v) {
@@ -357,7 +355,7 @@ int ttv_time_kernel(ttv_handle h, const char* name, int reps, int arg_i, float a
         else if (nm == "fgp_sweep") e.fgp_launch(FGP_SWEEP, fp, nullptr);
         else if (nm == "fgp_first") e.fgp_launch(FGP_FIRST, fp, nullptr);
         else if (nm == "fgp_final") e.fgp_launch(FGP_FINAL, fp, e.scratch.p);
-        else if (nm == "tv") { tv_value_kernel<<<(unsigned)((rows + 7) / 8), 256, 0, e.st>>>(e.recon.p, e.dims(), nullptr, e.d_red); ++e.launches; }
+        else if (nm == "tv") { tv_value_kernel<<<(unsigned)((rows + 7) / 8), 256, 0, e.st>>>(e.recon.p, e.dims(), nullptr, 1, e.d_red); ++e.launches; }
         else if (nm == "momentum") { momentum_kernel<<<ew_blocks(n / 4), 256, 0, e.st>>>(reinterpret_cast<float4*>(e.scratch.p), reinterpret_cast<float4*>(e.yk.p), reinterpret_cast<float4*>(e.recon_old.p), 0.5f, n / 4); ++e.launches; }
         else if (nm == "tvgd_grad") { tvgd_gradient_kernel<<<dim3(gsw.x, (e.N + 7) / 8, e.nxb), 256, 0, e.st>>>(gp); ++e.launches; }
         else if (nm == "tvgd_update") { tvgd_update_kernel<<<ew_blocks(n / 4), 256, 0, e.st>>>(e.yk.p, e.scratch.p, e.d_red + 1, 0.f, 0, n / 4); ++e.launches; }

@@ -158,6 +158,18 @@ __global__ void __launch_bounds__(256) gather_slice_kernel(const float* __restri
     for (int64_t m = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; m < M; m += (int64_t)gridDim.x * blockDim.x)
         plane[m] = src[((int64_t)xb * M + m) * 32 + xi];
 }
+// up to 4 slices -> planes in one launch (halo exchange of the FGP dual variables); blockIdx.y selects the job
+// dst element stride ds[q] / element offset de[q]: 1/0 = plain plane, 4/e = ghost cells [m][4] (ttv_fgp.cuh)
+struct GatherJobs { const float* src[4]; float* dst[4]; int x[4]; int ds[4]; int de[4]; int n; };
+__global__ void __launch_bounds__(256) gather_slices_kernel(const GatherJobs g, int64_t M)
+{
+    const int q = blockIdx.y;
+    const float* __restrict__ src = g.src[q];
+    float* __restrict__ plane = g.dst[q];
+    const int xb = g.x[q] >> 5, xi = g.x[q] & 31, ds = g.ds[q], de = g.de[q];
+    for (int64_t m = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; m < M; m += (int64_t)gridDim.x * blockDim.x)
+        plane[m * ds + de] = src[((int64_t)xb * M + m) * 32 + xi];
+}
 __global__ void __launch_bounds__(256) scatter_slice_kernel(float* __restrict__ dst, const float* __restrict__ plane, int x, int64_t M)
 {
     const int xb = x >> 5, xi = x & 31;

@@ -52,6 +52,20 @@ inline CUtensorMap make_tmap(const float* base, uint64_t d1, uint64_t d2, uint64
     return tm;
 }
 
+// 16-byte-cell map over a ghost array [N][N][4] float32 (ttv_fgp.cuh), addressed like the halo boxes
+inline CUtensorMap make_ghost_tmap(const float* base, uint64_t N, uint32_t b1, uint32_t b2) {
+    CUtensorMap tm;
+    cuuint64_t dims[4] = {4, N, N, 1};
+    cuuint64_t strides[3] = {16, 16 * N, 16 * N * N};
+    cuuint32_t box[4] = {4, b1, b2, 1};
+    cuuint32_t estr[4] = {1, 1, 1, 1};
+    CUresult r = get_encode_tiled()(&tm, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 4, const_cast<float*>(base), dims, strides, box, estr,
+                                    CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_NONE, CU_TENSOR_MAP_L2_PROMOTION_L2_128B,
+                                    CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    if (r != CUDA_SUCCESS) throw CudaError("cuTensorMapEncodeTiled (ghost) failed (code " + std::to_string((int)r) + ")");
+    return tm;
+}
+
 // ------------------------------------------------------------------------------------------
 // NCCL through dlopen (only touched when ttv_comm_init is called)
 // ------------------------------------------------------------------------------------------
@@ -508,41 +522,57 @@ public:
     // ---------------------------------------------------------------------------------------
     // halo planes (multi-GPU): ring / chain exchange of single slices over NCCL
     // ---------------------------------------------------------------------------------------
+    // 12 plain planes [j][k] followed by 10 ghost-cell arrays [j][k][4]
     float* plane(int i) {
         const size_t M = (size_t)N * N;
-        if (planes.n < 12 * M) planes.alloc(12 * M);
+        if (planes.n < 52 * M) planes.alloc(52 * M);
         return planes.p + (size_t)i * M;
     }
+    float* ghost(int i) { return plane(0) + (size_t)(12 + 4 * i) * N * N; }
     // send slice `xs` of `src` to rank `to`, receive a plane from rank `from` (either may be -1)
-    void exchange(const float* src, int xs, int to, float* sendbuf, int from, float* recvbuf) {
+    // ds/de: element stride / offset of the transferred layout (1/0 plain plane, 4/e ghost cells)
+    void exchange(const float* src, int xs, int to, float* sendbuf, int from, float* recvbuf, int ds = 1, int de = 0) {
         Nccl& n = Nccl::get();
         const int64_t M = (int64_t)N * N;
         ProfScope ps(*this, PF_HALO);
-        if (to >= 0) { gather_slice_kernel<<<256, 256, 0, st>>>(src, sendbuf, xs, M); ++launches; }
+        if (to >= 0) {
+            GatherJobs gj; gj.n = 1; gj.src[0] = src; gj.dst[0] = sendbuf; gj.x[0] = xs; gj.ds[0] = ds; gj.de[0] = de;
+            gather_slices_kernel<<<dim3(128, 1), 256, 0, st>>>(gj, M); ++launches;
+        }
         n.check(n.GroupStart(), "ncclGroupStart");
-        if (to >= 0) n.check(n.Send(sendbuf, M, Nccl::Float32, to, comm, st), "ncclSend");
-        if (from >= 0) n.check(n.Recv(recvbuf, M, Nccl::Float32, from, comm, st), "ncclRecv");
+        if (to >= 0) n.check(n.Send(sendbuf, M * ds, Nccl::Float32, to, comm, st), "ncclSend");
+        if (from >= 0) n.check(n.Recv(recvbuf, M * ds, Nccl::Float32, from, comm, st), "ncclRecv");
         n.check(n.GroupEnd(), "ncclGroupEnd");
     }
 
     // ---------------------------------------------------------------------------------------
     // regularisers
     // ---------------------------------------------------------------------------------------
-    double tv_value(const float* v) {
-        const float* hn = nullptr;
-        if (nranks > 1) {   // periodic ring: my slice 0 goes to the previous rank, I receive the next rank's slice 0
+    // TV value, stream-ordered: the reduction (and, sharded, its device-side all-reduce) lands in d_red[slot];
+    // fetch_red(slot) reads it later so callers sync once at their end.  `hn`: already exchanged
+    // slice (x_last+1) mod nxg, or nullptr to do the ring exchange here.
+    void tv_value_async(const float* v, int slot, const float* hn = nullptr, int hs = 1) {
+        if (nranks > 1 && !hn) {   // periodic ring: my slice 0 goes to the previous rank, I receive the next rank's slice 0
             exchange(v, 0, (rank - 1 + nranks) % nranks, plane(0), (rank + 1) % nranks, plane(1));
-            hn = plane(1);
+            hn = plane(1); hs = 1;
         }
-        zero_red(0);
+        zero_red(slot);
         const int64_t rows = (int64_t)nxb * N;
         {
             ProfScope ps(*this, PF_TV);
-            tv_value_kernel<<<(unsigned)((rows + 7) / 8), 256, 0, st>>>(v, dims(), hn, d_red); ++launches;
+            tv_value_kernel<<<(unsigned)((rows + 7) / 8), 256, 0, st>>>(v, dims(), hn, hs, d_red + slot); ++launches;
         }
         TTV_LAUNCH_CHECK();
-        return read_red(0);
+        if (nranks > 1) {
+            Nccl& nc = Nccl::get();
+            nc.check(nc.AllReduce(d_red + slot, d_red + slot, 1, Nccl::Float64, Nccl::Sum, comm, st), "ncclAllReduce");
+        }
     }
+    double fetch_red(int slot) {
+        double v; TTV_CUDA(cudaMemcpyAsync(&v, d_red + slot, sizeof(double), cudaMemcpyDeviceToHost, st)); sync();
+        return v;
+    }
+    double tv_value(const float* v) { tv_value_async(v, 0); return fetch_red(0); }
 
     // one tiled FGP launch (ttv_fgp.cuh); mode FGP_FIRST ignores P, FGP_FINAL writes D to `out`
     bool fgp_tiled = true;
@@ -557,6 +587,15 @@ public:
             tm.p2 = make_tmap(p.P2, N, N, nxb, FGP_CW, FGP_RJ); tm.p2h = make_tmap(p.P2, N, N, nxb, FGP_CW, FGP_RJ, 4);
             tm.p3 = make_tmap(p.P3, N, N, nxb, FGP_CW, FGP_RJ); tm.p3h = make_tmap(p.P3, N, N, nxb, FGP_CW, FGP_RJ, 4);
         }
+        tm.grin = tm.gr1 = tm.gr2 = tm.gr3 = tm.gl1 = tm.inh;              // placeholders when there is no neighbour
+        if (p.hr_in) tm.grin = make_ghost_tmap(p.hr_in, N, FGP_CW, FGP_RJ);
+        if (mode != FGP_FIRST) {
+            if (p.hr_in && p.hr_P1) {
+                tm.gr1 = make_ghost_tmap(p.hr_P1, N, FGP_CW, FGP_RJ); tm.gr2 = make_ghost_tmap(p.hr_P2, N, FGP_CW, FGP_RJ);
+                tm.gr3 = make_ghost_tmap(p.hr_P3, N, FGP_CW, FGP_RJ);
+            }
+            if (p.hl_P1) tm.gl1 = make_ghost_tmap(p.hl_P1, N, FGP_CW, FGP_RJ);
+        }
         const int seg = fgp_seg();
         dim3 grid(nxb, (N + FGP_TK - 1) / FGP_TK, (N + seg - 1) / seg);
         if (mode == FGP_FIRST) fgp_tile_kernel<FGP_FIRST><<<grid, FGP_THREADS, FGP_SMEM, st>>>(tm, p, out, seg);
@@ -569,41 +608,56 @@ public:
     float tv_fgp(int iter, float lambda) {
         use();
         const size_t n = vol_elems();
-        const float tv0 = (float)tv_value(recon.p);
+        // slice 0 of the right neighbour (ring): serves the periodic TV value, the TV map and -- on all but the
+        // last rank -- the non-periodic FGP chain (`in` is constant over the sweeps): one exchange per call
+        const float* hn = nullptr;
+        if (nranks > 1) { exchange(recon.p, 0, (rank - 1 + nranks) % nranks, ghost(0), (rank + 1) % nranks, ghost(1), 4, 0); hn = ghost(1); }
+        tv_value_async(recon.p, 0, hn, 4);
         if (!scratch.ok()) scratch.alloc(n);
         dim3 grid((N + TV_KSEG - 1) / TV_KSEG, (N + TV_WARPS - 1) / TV_WARPS, nxb);
         if (iter <= 0) {
-            const float* hn = nullptr;
-            if (nranks > 1) { exchange(recon.p, 0, (rank - 1 + nranks) % nranks, plane(0), (rank + 1) % nranks, plane(1)); hn = plane(1); }
             const int64_t rows = (int64_t)nxb * N;
-            tv_map_kernel<<<(unsigned)((rows + 7) / 8), 256, 0, st>>>(recon.p, scratch.p, dims(), hn); ++launches;
+            tv_map_kernel<<<(unsigned)((rows + 7) / 8), 256, 0, st>>>(recon.p, scratch.p, dims(), hn, 4); ++launches;
             std::swap(recon.p, scratch.p);
-            sync();
-            return tv0;
+            return (float)fetch_red(0);
         }
         for (int i = 0; i < 6; ++i) if (!P[i].ok() && iter > 1) P[i].alloc(n);
         FgpParams p;
         p.in = recon.p; p.lambda = lambda; p.multip = 1.0f / (26.0f * lambda); p.d = dims();
         p.hl_P1 = p.hr_in = p.hr_P1 = p.hr_P2 = p.hr_P3 = nullptr;
         const bool has_left = nranks > 1 && rank > 0, has_right = nranks > 1 && rank < nranks - 1;
-        if (nranks > 1) {
-            // `in` boundary slice is constant over the sweeps: one exchange (chain, non-periodic)
-            exchange(recon.p, 0, has_left ? rank - 1 : -1, plane(2), has_right ? rank + 1 : -1, plane(3));
-            if (has_right) p.hr_in = plane(3);
-        }
+        if (has_right) p.hr_in = hn;
         int cur = 0;   // P[cur*3 ..] holds the current dual variable
         for (int it = 0; it < iter; ++it) {
             const bool first = (it == 0), last = (it == iter - 1);
             if (!first) {
                 p.P1 = P[cur * 3 + 0].p; p.P2 = P[cur * 3 + 1].p; p.P3 = P[cur * 3 + 2].p;
                 if (nranks > 1) {
-                    // P1 of my last slice -> right neighbour (its x-1); P1..P3 of my first slice -> left neighbour (its x+1)
-                    exchange(p.P1, nx - 1, has_right ? rank + 1 : -1, plane(4), has_left ? rank - 1 : -1, plane(5));
-                    exchange(p.P1, 0, has_left ? rank - 1 : -1, plane(6), has_right ? rank + 1 : -1, plane(7));
-                    exchange(p.P2, 0, has_left ? rank - 1 : -1, plane(8), has_right ? rank + 1 : -1, plane(9));
-                    exchange(p.P3, 0, has_left ? rank - 1 : -1, plane(10), has_right ? rank + 1 : -1, plane(11));
-                    p.hl_P1 = has_left ? plane(5) : nullptr;
-                    if (has_right) { p.hr_P1 = plane(7); p.hr_P2 = plane(9); p.hr_P3 = plane(11); }
+                    // one gather launch + one NCCL group per sweep, in the ghost-cell layout the kernel's TMA boxes read:
+                    //   P1 of my last slice -> right neighbour (its x-1, element 3)       ghost 2 -> its ghost 3
+                    //   P1,P2,P3 of my first slice -> left neighbour (its x+1, element 0) ghosts 4,5,6 -> its ghosts 7,8,9
+                    const int64_t M = (int64_t)N * N;
+                    Nccl& nc = Nccl::get();
+                    ProfScope ps(*this, PF_HALO);
+                    GatherJobs gj; gj.n = 0;
+                    if (has_right) { gj.src[gj.n] = p.P1; gj.dst[gj.n] = ghost(2); gj.x[gj.n] = nx - 1; gj.ds[gj.n] = 4; gj.de[gj.n] = 3; ++gj.n; }
+                    if (has_left) {
+                        const float* srcs[3] = {p.P1, p.P2, p.P3};
+                        for (int q = 0; q < 3; ++q) { gj.src[gj.n] = srcs[q]; gj.dst[gj.n] = ghost(4 + q); gj.x[gj.n] = 0; gj.ds[gj.n] = 4; gj.de[gj.n] = 0; ++gj.n; }
+                    }
+                    if (gj.n > 0) { gather_slices_kernel<<<dim3(128, gj.n), 256, 0, st>>>(gj, M); ++launches; }
+                    nc.check(nc.GroupStart(), "ncclGroupStart");
+                    if (has_right) {
+                        nc.check(nc.Send(ghost(2), 4 * M, Nccl::Float32, rank + 1, comm, st), "ncclSend");
+                        nc.check(nc.Recv(ghost(7), 12 * M, Nccl::Float32, rank + 1, comm, st), "ncclRecv");
+                    }
+                    if (has_left) {
+                        nc.check(nc.Send(ghost(4), 12 * M, Nccl::Float32, rank - 1, comm, st), "ncclSend");
+                        nc.check(nc.Recv(ghost(3), 4 * M, Nccl::Float32, rank - 1, comm, st), "ncclRecv");
+                    }
+                    nc.check(nc.GroupEnd(), "ncclGroupEnd");
+                    p.hl_P1 = has_left ? ghost(3) : nullptr;
+                    if (has_right) { p.hr_P1 = ghost(7); p.hr_P2 = ghost(8); p.hr_P3 = ghost(9); }
                 }
             } else { p.P1 = p.P2 = p.P3 = nullptr; }
             if (last) {
@@ -626,23 +680,35 @@ public:
             TTV_LAUNCH_CHECK();
         }
         std::swap(recon.p, scratch.p);   // the volume is replaced by the last D (tv_fgp.cu:272)
-        sync();
-        return tv0;
+        return (float)fetch_red(0);
     }
 
     // cuda_tv_gd_3D, tv_gd.cu:141-218.  Returns TV of the input.
     float tv_gd(int ng, float dPOCS) {
         use();
         const size_t n = vol_elems();
-        const float tv0 = (float)tv_value(recon.p);
+        tv_value_async(recon.p, 0);
         if (!scratch.ok()) scratch.alloc(n);
         dim3 grid((N + TV_KSEG - 1) / TV_KSEG, (N + 7) / 8, nxb);
         for (int it = 0; it < ng; ++it) {
             GdParams p; p.x = recon.p; p.g = scratch.p; p.hm = p.hp = nullptr; p.sumsq = d_red + 1; p.d = dims();
             if (nranks > 1) {
-                exchange(recon.p, nx - 1, (rank + 1) % nranks, plane(0), (rank - 1 + nranks) % nranks, plane(1));
-                exchange(recon.p, 0, (rank - 1 + nranks) % nranks, plane(2), (rank + 1) % nranks, plane(3));
-                p.hm = plane(1); p.hp = plane(3);
+                // periodic ring, both directions, one gather launch + one NCCL group
+                const int64_t M = (int64_t)N * N;
+                const int up = (rank + 1) % nranks, dn = (rank - 1 + nranks) % nranks;
+                Nccl& nc = Nccl::get();
+                ProfScope ps(*this, PF_HALO);
+                GatherJobs gj; gj.n = 2;
+                gj.src[0] = recon.p; gj.dst[0] = plane(4); gj.x[0] = nx - 1; gj.ds[0] = 1; gj.de[0] = 0;
+                gj.src[1] = recon.p; gj.dst[1] = plane(6); gj.x[1] = 0; gj.ds[1] = 1; gj.de[1] = 0;
+                gather_slices_kernel<<<dim3(128, 2), 256, 0, st>>>(gj, M); ++launches;
+                nc.check(nc.GroupStart(), "ncclGroupStart");
+                nc.check(nc.Send(plane(4), M, Nccl::Float32, up, comm, st), "ncclSend");
+                nc.check(nc.Send(plane(6), M, Nccl::Float32, dn, comm, st), "ncclSend");
+                nc.check(nc.Recv(plane(5), M, Nccl::Float32, dn, comm, st), "ncclRecv");
+                nc.check(nc.Recv(plane(7), M, Nccl::Float32, up, comm, st), "ncclRecv");
+                nc.check(nc.GroupEnd(), "ncclGroupEnd");
+                p.hm = plane(5); p.hp = plane(7);
             }
             zero_red(1);
             {
@@ -661,8 +727,7 @@ public:
             TTV_LAUNCH_CHECK();
         }
         if (ng <= 0) { ew_kernel<EW_POS><<<ew_blocks(n / 4), 256, 0, st>>>(reinterpret_cast<float4*>(recon.p), 0.f, n / 4); ++launches; }
-        sync();
-        return tv0;
+        return (float)fetch_red(0);
     }
 
     template <int OP> double reduce(const float* a, const float* bb, size_t n) {

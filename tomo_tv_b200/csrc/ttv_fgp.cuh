@@ -42,7 +42,10 @@ constexpr size_t FGP_SMEM = (size_t)FGP_NS * FGP_STAGE + (size_t)FGP_DR * 32 * 1
 
 enum FgpMode { FGP_SWEEP = 0, FGP_FIRST = 1, FGP_FINAL = 2 };
 
-struct FgpMaps { CUtensorMap in, p1, p2, p3, inh, p1h, p2h, p3h; };
+// main boxes, 16-byte halo boxes over the same arrays, and -- for a slab of a sharded volume -- the
+// ghost cells [j][k][4] received from the neighbouring ranks (gr*: right neighbour's slice 0 in
+// element 0; gl1: left neighbour's last slice of P1 in element 3).  has_gr / has_gl say whether they exist.
+struct FgpMaps { CUtensorMap in, p1, p2, p3, inh, p1h, p2h, p3h, grin, gr1, gr2, gr3, gl1; };
 
 template <int MODE>
 __global__ void __launch_bounds__(FGP_THREADS, 1)
@@ -63,7 +66,8 @@ fgp_tile_kernel(const __grid_constant__ FgpMaps tm, const FgpParams p, float* __
     const int nx = p.d.nx;
     const bool lastblk = (xb == p.d.nxb - 1);
     const int edge_lane = lastblk ? ((nx - 1) & 31) : 31;
-    const bool has_xp = !lastblk || (p.hr_in != nullptr);
+    const bool has_xp = !lastblk || (p.hr_in != nullptr);     // a slice x+1 exists for the block's edge lane
+    const bool has_xm = xb > 0 || (p.hl_P1 != nullptr);       // a slice x-1 exists for lane 0
     const float lambda = p.lambda, multip = p.multip;
 
     if (tid == 0) {
@@ -86,9 +90,9 @@ fgp_tile_kernel(const __grid_constant__ FgpMaps tm, const FgpParams p, float* __
             // box ids: 0..3 main in,P1,P2,P3 ; 4..7 x+1 halo in,P1,P2,P3 ; 8 x-1 halo P1
             bool want = false;
             if (lane < 9) {
-                if (MODE == FGP_FIRST) want = (lane == 0) || (lane == 4 && !lastblk);
-                else if (MODE == FGP_FINAL) want = (lane < 4) || (lane == 8 && xb > 0);
-                else want = (lane < 4) || (lane < 8 && !lastblk) || (lane == 8 && xb > 0);
+                if (MODE == FGP_FIRST) want = (lane == 0) || (lane == 4 && has_xp);
+                else if (MODE == FGP_FINAL) want = (lane < 4) || (lane == 8 && has_xm);
+                else want = (lane < 4) || (lane < 8 && has_xp) || (lane == 8 && has_xm);
             }
             if (want) {
                 const int id = lane;
@@ -97,10 +101,17 @@ fgp_tile_kernel(const __grid_constant__ FgpMaps tm, const FgpParams p, float* __
                     tma_load_4d(sb + (size_t)id * FGP_MAIN_ARR, m, &full[buf], 0, k0 - 1, row, xb);
                 } else if (id < 8) {
                     const int a = id - 4;
-                    const CUtensorMap* m = a == 0 ? &tm.inh : a == 1 ? &tm.p1h : a == 2 ? &tm.p2h : &tm.p3h;
-                    tma_load_4d(sb + 4 * FGP_MAIN_ARR + (size_t)a * FGP_HALO_ARR, m, &full[buf], 0, k0 - 1, row, xb + 1);
-                } else {
+                    if (!lastblk) {
+                        const CUtensorMap* m = a == 0 ? &tm.inh : a == 1 ? &tm.p1h : a == 2 ? &tm.p2h : &tm.p3h;
+                        tma_load_4d(sb + 4 * FGP_MAIN_ARR + (size_t)a * FGP_HALO_ARR, m, &full[buf], 0, k0 - 1, row, xb + 1);
+                    } else {
+                        const CUtensorMap* m = a == 0 ? &tm.grin : a == 1 ? &tm.gr1 : a == 2 ? &tm.gr2 : &tm.gr3;
+                        tma_load_4d(sb + 4 * FGP_MAIN_ARR + (size_t)a * FGP_HALO_ARR, m, &full[buf], 0, k0 - 1, row, 0);
+                    }
+                } else if (xb > 0) {
                     tma_load_4d(sb + 4 * FGP_MAIN_ARR + 4 * FGP_HALO_ARR, &tm.p1h, &full[buf], 28, k0 - 1, row, xb - 1);
+                } else {
+                    tma_load_4d(sb + 4 * FGP_MAIN_ARR + 4 * FGP_HALO_ARR, &tm.gl1, &full[buf], 0, k0 - 1, row, 0);
                 }
             }
             const unsigned m = __ballot_sync(0xffffffffu, want);
@@ -119,36 +130,20 @@ fgp_tile_kernel(const __grid_constant__ FgpMaps tm, const FgpParams p, float* __
                 mbar_wait(&full[buf], (it / FGP_NS) & 1);
                 const uint32_t sb = s_stage + buf * FGP_STAGE;
                 const int rowbase = ja - 1 + it * FGP_RJ;
-                const int k = k0 + lane;
 #pragma unroll
                 for (int r = 0; r < FGP_RJ; ++r) {
                     const int j = rowbase + r;
-                    float D = 0.0f;
-                    if (!lastblk) {
-                        const uint32_t hb = sb + 4 * FGP_MAIN_ARR + (uint32_t)(r * FGP_CW + lane + 1) * 16u;
-                        const float inn = lds32(hb);
-                        if (MODE == FGP_FIRST) D = fmaxf(inn, 0.0f);
-                        else {
-                            const float q1 = lds32(hb + FGP_HALO_ARR), q2 = lds32(hb + 2 * FGP_HALO_ARR), q3 = lds32(hb + 3 * FGP_HALO_ARR);
-                            const float v3 = lds32(hb + 3 * FGP_HALO_ARR - 16u);
-                            const float v1 = lds32(sb + FGP_MAIN_ARR + (uint32_t)(r * FGP_CW + lane + 1) * 128u + 124u);
-                            const float sum = ((((q1 + q2) + q3) - v1) - hq2) - v3;
-                            D = fmaxf(__fmaf_rn(-lambda, sum, inn), 0.0f);
-                            hq2 = q2;
-                        }
-                    } else if (j >= 0 && j < N && k < N) {
-                        // right halo planes of the neighbouring rank (slab decomposition)
-                        const int64_t jk = (int64_t)j * N + k;
-                        const float inn = p.hr_in[jk];
-                        if (MODE == FGP_FIRST) D = fmaxf(inn, 0.0f);
-                        else {
-                            const float q1 = p.hr_P1[jk], q2 = p.hr_P2[jk], q3 = p.hr_P3[jk];
-                            const float v2 = j > 0 ? p.hr_P2[jk - N] : 0.0f;
-                            const float v3 = k > 0 ? p.hr_P3[jk - 1] : 0.0f;
-                            const float v1 = lds32(sb + FGP_MAIN_ARR + (uint32_t)(r * FGP_CW + lane + 1) * 128u + (uint32_t)edge_lane * 4u);
-                            const float sum = ((((q1 + q2) + q3) - v1) - v2) - v3;
-                            D = fmaxf(__fmaf_rn(-lambda, sum, inn), 0.0f);
-                        }
+                    float D;
+                    const uint32_t hb = sb + 4 * FGP_MAIN_ARR + (uint32_t)(r * FGP_CW + lane + 1) * 16u;
+                    const float inn = lds32(hb);
+                    if (MODE == FGP_FIRST) D = fmaxf(inn, 0.0f);
+                    else {
+                        const float q1 = lds32(hb + FGP_HALO_ARR), q2 = lds32(hb + 2 * FGP_HALO_ARR), q3 = lds32(hb + 3 * FGP_HALO_ARR);
+                        const float v3 = lds32(hb + 3 * FGP_HALO_ARR - 16u);
+                        const float v1 = lds32(sb + FGP_MAIN_ARR + (uint32_t)(r * FGP_CW + lane + 1) * 128u + (uint32_t)edge_lane * 4u);
+                        const float sum = ((((q1 + q2) + q3) - v1) - hq2) - v3;
+                        D = fmaxf(__fmaf_rn(-lambda, sum, inn), 0.0f);
+                        hq2 = q2;
                     }
                     sts32(s_X + (uint32_t)(((j & (FGP_DR - 1)) * 32 + lane) * 4), D);
                 }
@@ -161,7 +156,6 @@ fgp_tile_kernel(const __grid_constant__ FgpMaps tm, const FgpParams p, float* __
     // ---------------- compute warps: columns c = warp and warp + 16 of the k-tile ----------------
     const bool valid = xb * 32 + lane < nx;
     const bool x_ok = valid && (lane != edge_lane || has_xp);   // the x-difference exists for this lane
-    const bool use_hl = (xb == 0) && (p.hl_P1 != nullptr);      // left halo plane of the neighbouring rank
     const uint32_t tc = (uint32_t)(warp + 1) * 128u + (uint32_t)lane * 4u;
     bool pk[2];
     pk[0] = (k0 + warp < N);
@@ -196,15 +190,11 @@ fgp_tile_kernel(const __grid_constant__ FgpMaps tm, const FgpParams p, float* __
                 } else {
                     const float p1 = lds32(a + FGP_MAIN_ARR), p2 = lds32(a + 2 * FGP_MAIN_ARR), p3 = lds32(a + 3 * FGP_MAIN_ARR);
                     const float v3 = lds32(a + 3 * FGP_MAIN_ARR - 128u);
-                    // slice 31 of x-block xb-1 (broadcast read; only lane 0 uses it)
+                    // slice 31 of x-block xb-1 / the left ghost cell (broadcast read; only lane 0 uses it)
                     const float hv = lds32(s_stage + buf * FGP_STAGE + 4 * FGP_MAIN_ARR + 4 * FGP_HALO_ARR
                                            + (uint32_t)(r * FGP_CW + warp + 1 + h * 16) * 16u + 12u);
                     float v1 = __shfl_up_sync(0xffffffffu, p1, 1);
-                    if (lane == 0) v1 = (xb > 0) ? hv : 0.0f;
-                    if (use_hl) {
-                        const int j = rowbase + r, k = k0 + warp + h * 16;
-                        if (lane == 0 && j >= 0 && j < N && k < N) v1 = p.hl_P1[(int64_t)j * N + k];
-                    }
+                    if (lane == 0) v1 = has_xm ? hv : 0.0f;
                     const float v2 = (r == 0) ? cP2[h] : P2[h][0];
                     const float sum = ((((p1 + p2) + p3) - v1) - v2) - v3;
                     P1[h][r] = p1; P2[h][r] = p2; P3[h][r] = p3;

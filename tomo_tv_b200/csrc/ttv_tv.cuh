@@ -12,8 +12,9 @@
 // that reads in,P1,P2,P3 once and writes P1,P2,P3 once.
 //
 // Multi-GPU: a rank holds a slab of slices; `xoff`/`nxg` give its position in the global
-// volume and the halo planes ([j][k] row-major, one slice each) carry the neighbours' boundary
-// slices.
+// volume.  Neighbour boundary slices arrive either as plain planes ([j][k], TV-GD) or as ghost
+// cells ([j][k][4] floats = the 16-byte TMA box of ttv_fgp.cuh: the right neighbour's slice 0 in
+// element 0, the left neighbour's last slice in element 3); see DESIGN.md.
 #pragma once
 #include "ttv_common.cuh"
 
@@ -38,7 +39,7 @@ __device__ __forceinline__ float x_minus1(float line, const float* __restrict__ 
     float v = __shfl_up_sync(0xffffffffu, line, 1);
     if (lane == 0) {
         if (xb > 0) v = ptr[(cell - cellsPerBlock) * TTV_XI + 31];
-        else v = halo_left ? halo_left[jk] : 0.0f;
+        else v = halo_left ? halo_left[jk * 4 + 3] : 0.0f;
     }
     return v;
 }
@@ -47,7 +48,7 @@ __device__ __forceinline__ float x_minus1(float line, const float* __restrict__ 
 // TV value: sum sqrt(eps + dx^2 + dy^2 + dz^2), periodic forward differences.
 // halo_next: slice (x_last+1) mod nxg when the rank does not own it (NULL on one GPU).
 // ---------------------------------------------------------------------------------------------
-__global__ void __launch_bounds__(256) tv_value_kernel(const float* __restrict__ v, VolDims d, const float* __restrict__ halo_next, double* out)
+__global__ void __launch_bounds__(256) tv_value_kernel(const float* __restrict__ v, VolDims d, const float* __restrict__ halo_next, int hs, double* out)
 {
     const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
     const int N = d.N;
@@ -68,7 +69,7 @@ __global__ void __launch_bounds__(256) tv_value_kernel(const float* __restrict__
             if (valid) {
                 if (x == d.nx - 1) {
                     // last local slice: neighbour is global (x+1) mod nxg
-                    if (halo_next) vx = halo_next[(int64_t)j * N + k];
+                    if (halo_next) vx = halo_next[((int64_t)j * N + k) * hs];
                     else vx = v[((int64_t)j * N + k) * 32 + 0];                 // wraps to local slice 0
                 } else if (lane == 31) {
                     vx = v[(cell + cpb) * 32 + 0];
@@ -93,8 +94,8 @@ __global__ void __launch_bounds__(256) tv_value_kernel(const float* __restrict__
 // TV-FGP sweep.
 //   D(p)  = max(0, in(p) - lambda*(P1+P2+P3 - P1(x-1) - P2(j-1) - P3(k-1)))        tv_fgp.cu:44-65,143-154
 //   Pn(p) = proj( P + multip * (D(p) - D(p+e)) ), zero difference on the high edge  tv_fgp.cu:67-115
-// FIRST: P == 0 (first sweep, no P loads).  Halo planes for a slab (NULL on a single GPU):
-//   hl_P1: P1 of global slice xoff-1;  hr_in/hr_P1/hr_P2/hr_P3: slice xoff+nx of in and P.
+// FIRST: P == 0 (first sweep, no P loads).  Ghost cells for a slab (NULL on a single GPU), [j][k][4]:
+//   hl_P1: P1 of global slice xoff-1 (element 3);  hr_in/hr_P1/hr_P2/hr_P3: slice xoff+nx of in and P (element 0).
 // ---------------------------------------------------------------------------------------------
 struct FgpParams {
     const float* in;
@@ -128,11 +129,11 @@ __device__ __forceinline__ float fgp_D_xplus(const FgpParams& p, int64_t cell, i
     const int64_t jk = (int64_t)j * N + k;
     float inn, q1 = 0.f, q2 = 0.f, q3 = 0.f, v2 = 0.f, v3 = 0.f;
     if (from_halo) {
-        inn = p.hr_in[jk];
+        inn = p.hr_in[jk * 4];
         if (!FIRST) {
-            q1 = p.hr_P1[jk]; q2 = p.hr_P2[jk]; q3 = p.hr_P3[jk];
-            v2 = j > 0 ? p.hr_P2[jk - N] : 0.f;
-            v3 = k > 0 ? p.hr_P3[jk - 1] : 0.f;
+            q1 = p.hr_P1[jk * 4]; q2 = p.hr_P2[jk * 4]; q3 = p.hr_P3[jk * 4];
+            v2 = j > 0 ? p.hr_P2[(jk - N) * 4] : 0.f;
+            v3 = k > 0 ? p.hr_P3[(jk - 1) * 4] : 0.f;
         }
     } else {
         const int64_t c2 = (cell + cpb) * 32;   // lane 0 of the next block
@@ -236,7 +237,7 @@ __global__ void __launch_bounds__(256) fgp_final_kernel(const FgpParams p, float
 }
 
 // tv_fgp(iter = 0): the reference returns the TV *map* in place of the volume (tv_fgp.cu:232,272)
-__global__ void __launch_bounds__(256) tv_map_kernel(const float* __restrict__ v, float* __restrict__ out, VolDims d, const float* __restrict__ halo_next)
+__global__ void __launch_bounds__(256) tv_map_kernel(const float* __restrict__ v, float* __restrict__ out, VolDims d, const float* __restrict__ halo_next, int hs)
 {
     const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
     const int N = d.N;
@@ -255,7 +256,7 @@ __global__ void __launch_bounds__(256) tv_map_kernel(const float* __restrict__ v
         float vx = __shfl_down_sync(0xffffffffu, c, 1);
         float r = 0.f;
         if (valid) {
-            if (x == d.nx - 1) vx = halo_next ? halo_next[(int64_t)j * N + k] : v[((int64_t)j * N + k) * 32];
+            if (x == d.nx - 1) vx = halo_next ? halo_next[((int64_t)j * N + k) * hs] : v[((int64_t)j * N + k) * 32];
             else if (lane == 31) vx = v[(cell + cpb) * 32];
             const float dx = c - vx, dy = c - vj, dz = c - vk;
             r = sqrtf(1e-6f + dx * dx + dy * dy + dz * dz);
