@@ -169,9 +169,7 @@ def run_ours(args):
     ang = np.deg2rad(tilt_angles_deg(na)).astype(np.float32)
     eng = ttv.tomoengine(nloc, n, ang, device=local, x_offset=x0, nslice_global=n)
     if world > 1:
-        uid = [ttv.tomoengine.nccl_unique_id() if rank == 0 else None]
-        dist.broadcast_object_list(uid, src=0)
-        eng.comm_init(uid[0], rank, world)
+        eng.setup_sharding(dist, rank, world, p2p=os.environ.get("TTV_P2P", "1") != "0")
 
     # synthetic data: phantom slab -> tilt series by the engine's own forward projector
     vol = phantom3d(n, n, x0=x0, count=nloc)

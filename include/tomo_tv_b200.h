@@ -101,6 +101,19 @@ int ttv_rmse(ttv_handle h, float* v);                                           
 int ttv_nccl_unique_id(void* id128);                       /* rank 0: 128-byte ncclUniqueId to broadcast */
 int ttv_comm_init(ttv_handle h, const void* id128, int rank, int nranks);
 
+/* Peer-memory halo hand-off for TV-FGP (optional, same node): every rank exports a 64-byte CUDA IPC
+ * handle of its ghost-plane buffer, the handles are exchanged by the launcher (e.g. torch.distributed
+ * all_gather) and each rank attaches its left / right neighbour's (NULL at the ends of the chain).
+ * The sweep kernel then stores its boundary slices directly into the neighbours' HBM over NVLink and
+ * publishes an epoch flag; no NCCL call is left on the per-sweep path. */
+int ttv_p2p_export(ttv_handle h, void* handle64);
+int ttv_p2p_attach(ttv_handle h, const void* left_handle64, const void* right_handle64);
+/* same hand-off between engines living in ONE process (plain device pointers instead of IPC handles);
+ * ttv_set_rank gives such an engine its position in the chain without an NCCL communicator -- the
+ * caller then drives the slab engines from one host thread each (tests: two slabs on one GPU). */
+int ttv_p2p_attach_local(ttv_handle h, ttv_handle left, ttv_handle right);
+int ttv_set_rank(ttv_handle h, int rank, int nranks);
+
 /* --- measurement / test hooks (not part of the reference API) ------------------------------- */
 int ttv_sync(ttv_handle h);
 /* device-side __cosf/__sinf of the per-angle FP angle, as the projector evaluates them */

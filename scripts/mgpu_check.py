@@ -47,9 +47,7 @@ def run(eng, v):
 
 x0, cnt = slab_bounds(nx, world, rank)
 eng = ttv.tomoengine(cnt, n, ang, device=local, x_offset=x0, nslice_global=nx)
-uid = [ttv.tomoengine.nccl_unique_id() if rank == 0 else None]
-dist.broadcast_object_list(uid, src=0)
-eng.comm_init(uid[0], rank, world)
+eng.setup_sharding(dist, rank, world, p2p=os.environ.get("TTV_P2P", "1") != "0")
 mine = run(eng, vol[x0:x0 + cnt])
 gathered = [None] * world
 dist.all_gather_object(gathered, {k: v for k, v in mine.items()})

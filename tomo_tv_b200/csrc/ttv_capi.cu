@@ -276,6 +276,16 @@ int ttv_comm_init(ttv_handle h, const void* id128, int rank, int nranks) {
     TTV_CATCH
 }
 
+int ttv_p2p_export(ttv_handle h, void* handle64) { TTV_TRY E(h).p2p_export(handle64); TTV_CATCH }
+int ttv_p2p_attach(ttv_handle h, const void* left64, const void* right64) { TTV_TRY E(h).p2p_attach(left64, right64); TTV_CATCH }
+
+int ttv_p2p_attach_local(ttv_handle h, ttv_handle left, ttv_handle right) {
+    TTV_TRY
+    E(h).p2p_attach_local(left ? left->e : nullptr, right ? right->e : nullptr);
+    TTV_CATCH
+}
+int ttv_set_rank(ttv_handle h, int rank, int nranks) { TTV_TRY Engine& e = E(h); e.rank = rank; e.nranks = nranks; TTV_CATCH }
+
 // ------------------------------------------------------------------ measurement / test hooks
 int ttv_sync(ttv_handle h) { TTV_TRY E(h).sync(); TTV_CATCH }
 int ttv_get_trig(ttv_handle h, float* cosv, float* sinv) {
@@ -339,6 +349,7 @@ int ttv_time_kernel(ttv_handle h, const char* name, int reps, int arg_i, float a
     if (!e.recon_old.ok()) e.recon_old.alloc(n);
     if (e.Na > 0) e.compute_weights();
     FgpParams fp; fp.in = e.recon.p; fp.P1 = e.P[0].p; fp.P2 = e.P[1].p; fp.P3 = e.P[2].p; fp.Q1 = e.P[3].p; fp.Q2 = e.P[4].p; fp.Q3 = e.P[5].p;
+    fp.compact = 0; fp.pitch = 0; fp.rm_gl1 = fp.rm_gr1 = fp.rm_gr2 = fp.rm_gr3 = nullptr; fp.rm_flagR = fp.rm_flagL = nullptr; fp.cnt = nullptr; fp.epoch = 0;
     fp.hl_P1 = fp.hr_in = fp.hr_P1 = fp.hr_P2 = fp.hr_P3 = nullptr; fp.lambda = 0.1f; fp.multip = 1.0f / 2.6f; fp.d = e.dims();
     dim3 gsw((e.N + TV_KSEG - 1) / TV_KSEG, (e.N + TV_WARPS - 1) / TV_WARPS, e.nxb);
     GdParams gp; gp.x = e.recon.p; gp.g = e.scratch.p; gp.hm = gp.hp = nullptr; gp.sumsq = e.d_red + 1; gp.d = e.dims();

@@ -66,6 +66,54 @@ inline CUtensorMap make_ghost_tmap(const float* base, uint64_t N, uint32_t b1, u
     return tm;
 }
 
+// map over a compact ghost plane [N][pitch] float32 (peer-memory hand-off, ttv_fgp.cuh): box = 36 floats x rows
+inline CUtensorMap make_plane_tmap(const float* base, uint64_t N, uint64_t pitch, uint32_t b0, uint32_t b1) {
+    CUtensorMap tm;
+    cuuint64_t dims[4] = {N, N, 1, 1};
+    cuuint64_t strides[3] = {4 * pitch, 4 * pitch * N, 4 * pitch * N};
+    cuuint32_t box[4] = {b0, b1, 1, 1};
+    cuuint32_t estr[4] = {1, 1, 1, 1};
+    CUresult r = get_encode_tiled()(&tm, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 4, const_cast<float*>(base), dims, strides, box, estr,
+                                    CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_NONE, CU_TENSOR_MAP_L2_PROMOTION_L2_128B,
+                                    CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    if (r != CUDA_SUCCESS) throw CudaError("cuTensorMapEncodeTiled (plane) failed (code " + std::to_string((int)r) + ")");
+    return tm;
+}
+
+// spin until the neighbours have published `epoch` (they write these flags into this GPU's memory at the
+// end of their sweep); bounded so a lost peer cannot hang the device
+__global__ void wait_flags_kernel(const unsigned* fl, const unsigned* fr, unsigned epoch, int* err)
+{
+    const long long t0 = clock64();
+    for (int side = 0; side < 2; ++side) {
+        const unsigned* f = side == 0 ? fl : fr;
+        if (!f) continue;
+        for (;;) {
+            unsigned v;
+            asm volatile("ld.acquire.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(f) : "memory");
+            if ((int)(v - epoch) >= 0) break;
+            if (clock64() - t0 > 4000000000LL) { err[0] = 1; err[1] = side; err[2] = (int)v; err[3] = (int)epoch; return; }
+            __nanosleep(200);
+        }
+    }
+}
+
+// store slice x of an interleaved array into a (possibly remote, peer-mapped) buffer dst[m*ds + de] and, once
+// every block's stores are performed system-wide, publish `epoch` on the owner of dst
+__global__ void __launch_bounds__(256) push_slice_kernel(const float* __restrict__ src, int x, float* __restrict__ dst, int ds, int de, int64_t M,
+                                                         unsigned* cnt, unsigned* rm_flag, unsigned epoch)
+{
+    const int xb = x >> 5, xi = x & 31;
+    for (int64_t m = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; m < M; m += (int64_t)gridDim.x * blockDim.x)
+        dst[m * ds + de] = src[((int64_t)xb * M + m) * 32 + xi];
+    __threadfence_system();
+    __syncthreads();
+    if (threadIdx.x == 0 && atomicAdd(cnt, 1u) == gridDim.x - 1) {
+        *cnt = 0; __threadfence_system();
+        asm volatile("st.release.sys.global.u32 [%0], %1;" ::"l"(rm_flag), "r"(epoch) : "memory");
+    }
+}
+
 // ------------------------------------------------------------------------------------------
 // NCCL through dlopen (only touched when ttv_comm_init is called)
 // ------------------------------------------------------------------------------------------
@@ -101,11 +149,14 @@ struct Nccl {
 
 struct DBuf {
     float* p = nullptr; size_t n = 0;
+    // cudaMemset on device memory is asynchronous on the legacy stream, which the engine's non-blocking
+    // stream does not order against: wait for it here, or it could land after later kernels' writes
     void alloc(size_t count) {
-        if (p && n == count) { TTV_CUDA(cudaMemset(p, 0, n * sizeof(float))); return; }
+        if (p && n == count) { TTV_CUDA(cudaMemset(p, 0, n * sizeof(float))); TTV_CUDA(cudaStreamSynchronize(cudaStreamLegacy)); return; }
         release();
         TTV_CUDA(cudaMalloc(&p, count * sizeof(float))); n = count;
         TTV_CUDA(cudaMemset(p, 0, n * sizeof(float)));
+        TTV_CUDA(cudaStreamSynchronize(cudaStreamLegacy));
     }
     void release() { if (p) cudaFree(p); p = nullptr; n = 0; }
     bool ok() const { return p != nullptr; }
@@ -196,6 +247,55 @@ public:
 
     // comm
     Nccl::comm_t comm = nullptr; int rank = 0, nranks = 1;
+    // peer-memory hand-off (CUDA IPC): [256 B flags+counters][8 compact planes gl1[2], gr1[2], gr2[2], gr3[2]]
+    float* p2p_base = nullptr; float* p2p_left = nullptr; float* p2p_right = nullptr;
+    bool p2p_ready = false; unsigned fgp_epoch = 0; int p2p_pitch = 0;
+    int* d_err = nullptr;
+    size_t p2p_plane_elems() const { return (size_t)N * p2p_pitch; }
+    size_t p2p_bytes() const { return 256 + (8 * p2p_plane_elems() + 2 * (size_t)N * N * 4) * sizeof(float); }
+    // ghost-cell array [N][N][4] holding slice 0 of `in` of the right (ring) neighbour, double-buffered
+    static float* p2p_grin(float* base, size_t pe, size_t M, int parity) { return base + 64 + 8 * pe + (size_t)parity * M * 4; }
+    unsigned in_epoch = 0;
+    static float* p2p_plane(float* base, size_t pe, int arr, int parity) { return base + 64 + (size_t)(arr * 2 + parity) * pe; }   // arr: 0 gl1, 1..3 gr1..3
+    static unsigned* p2p_flag(float* base, int which) { return reinterpret_cast<unsigned*>(base) + which; }   // 0: from left, 1: from right, 2,3: counters
+    void p2p_export(void* handle64) {
+        p2p_alloc();
+        cudaIpcMemHandle_t h;
+        TTV_CUDA(cudaIpcGetMemHandle(&h, p2p_base));
+        static_assert(sizeof(h) == 64, "cudaIpcMemHandle_t is 64 bytes");
+        std::memcpy(handle64, &h, 64);
+    }
+    bool p2p_local = false;
+    void p2p_alloc() {
+        use();
+        if (p2p_base) return;
+        p2p_pitch = (N + 3) & ~3;
+        TTV_CUDA(cudaMalloc(&p2p_base, p2p_bytes()));
+        TTV_CUDA(cudaMemset(p2p_base, 0, p2p_bytes()));
+        TTV_CUDA(cudaMalloc(&d_err, 4 * sizeof(int)));
+        TTV_CUDA(cudaMemset(d_err, 0, 4 * sizeof(int)));
+        TTV_CUDA(cudaStreamSynchronize(cudaStreamLegacy));
+    }
+    // neighbours living in the same process (tests, single-process multi-GPU): plain pointers, no IPC
+    void p2p_attach_local(Engine* left, Engine* right) {
+        p2p_alloc();
+        if (left) { left->p2p_alloc(); p2p_left = left->p2p_base; }
+        if (right) { right->p2p_alloc(); p2p_right = right->p2p_base; }
+        p2p_local = true; p2p_ready = true;
+    }
+    void p2p_attach(const void* left64, const void* right64) {
+        use();
+        if (!p2p_base) throw CudaError("p2p_attach before p2p_export");
+        auto open = [&](const void* h64) -> float* {
+            cudaIpcMemHandle_t h; std::memcpy(&h, h64, 64);
+            void* ptr = nullptr;
+            TTV_CUDA(cudaIpcOpenMemHandle(&ptr, h, cudaIpcMemLazyEnablePeerAccess));
+            return static_cast<float*>(ptr);
+        };
+        if (left64) p2p_left = open(left64);
+        if (right64) p2p_right = open(right64);
+        p2p_ready = true;
+    }
 
     Engine(int nslice, int nray, const float* ang, int nang, int dev, int x_offset, int nslice_global)
         : nx(nslice), N(nray), xoff(x_offset), nxg(nslice_global)
@@ -221,6 +321,9 @@ public:
     }
     ~Engine() {
         cudaSetDevice(device);
+        if (p2p_left && !p2p_local) cudaIpcCloseMemHandle(p2p_left);
+        if (p2p_right && !p2p_local) cudaIpcCloseMemHandle(p2p_right);
+        cudaFree(p2p_base); cudaFree(d_err);
         if (comm) Nccl::get().CommDestroy(comm);
         for (DBuf* d : {&recon, &yk, &recon_old, &temp, &original, &b, &g, &r, &scratch, &R, &C, &stage, &planes}) d->release();
         for (auto& d : P) d.release();
@@ -563,7 +666,7 @@ public:
             tv_value_kernel<<<(unsigned)((rows + 7) / 8), 256, 0, st>>>(v, dims(), hn, hs, d_red + slot); ++launches;
         }
         TTV_LAUNCH_CHECK();
-        if (nranks > 1) {
+        if (nranks > 1 && comm) {   // (same-process slab engines without a communicator return their partial sum)
             Nccl& nc = Nccl::get();
             nc.check(nc.AllReduce(d_red + slot, d_red + slot, 1, Nccl::Float64, Nccl::Sum, comm, st), "ncclAllReduce");
         }
@@ -591,10 +694,15 @@ public:
         if (p.hr_in) tm.grin = make_ghost_tmap(p.hr_in, N, FGP_CW, FGP_RJ);
         if (mode != FGP_FIRST) {
             if (p.hr_in && p.hr_P1) {
-                tm.gr1 = make_ghost_tmap(p.hr_P1, N, FGP_CW, FGP_RJ); tm.gr2 = make_ghost_tmap(p.hr_P2, N, FGP_CW, FGP_RJ);
-                tm.gr3 = make_ghost_tmap(p.hr_P3, N, FGP_CW, FGP_RJ);
+                if (p.compact) {
+                    tm.gr1 = make_plane_tmap(p.hr_P1, N, p.pitch, FGP_PB, FGP_RJ); tm.gr2 = make_plane_tmap(p.hr_P2, N, p.pitch, FGP_PB, FGP_RJ);
+                    tm.gr3 = make_plane_tmap(p.hr_P3, N, p.pitch, FGP_PB, FGP_RJ);
+                } else {
+                    tm.gr1 = make_ghost_tmap(p.hr_P1, N, FGP_CW, FGP_RJ); tm.gr2 = make_ghost_tmap(p.hr_P2, N, FGP_CW, FGP_RJ);
+                    tm.gr3 = make_ghost_tmap(p.hr_P3, N, FGP_CW, FGP_RJ);
+                }
             }
-            if (p.hl_P1) tm.gl1 = make_ghost_tmap(p.hl_P1, N, FGP_CW, FGP_RJ);
+            if (p.hl_P1) tm.gl1 = p.compact ? make_plane_tmap(p.hl_P1, N, p.pitch, FGP_PB, FGP_RJ) : make_ghost_tmap(p.hl_P1, N, FGP_CW, FGP_RJ);
         }
         const int seg = fgp_seg();
         dim3 grid(nxb, (N + FGP_TK - 1) / FGP_TK, (N + seg - 1) / seg);
@@ -608,10 +716,27 @@ public:
     float tv_fgp(int iter, float lambda) {
         use();
         const size_t n = vol_elems();
+        // every allocation first: cudaMalloc may synchronise the device, which must not happen while a
+        // wait kernel of this call spins on a neighbour's epoch
+        if (!scratch.ok()) scratch.alloc(n);
+        for (int i = 0; i < 6; ++i) if (!P[i].ok() && iter > 1) P[i].alloc(n);
         // slice 0 of the right neighbour (ring): serves the periodic TV value, the TV map and -- on all but the
         // last rank -- the non-periodic FGP chain (`in` is constant over the sweeps): one exchange per call
         const float* hn = nullptr;
-        if (nranks > 1) { exchange(recon.p, 0, (rank - 1 + nranks) % nranks, ghost(0), (rank + 1) % nranks, ghost(1), 4, 0); hn = ghost(1); }
+        const bool p2p = nranks > 1 && p2p_ready && fgp_tiled;
+        const size_t pe = p2p ? p2p_plane_elems() : 0;
+        if (p2p) {
+            // peer memory: my slice 0 goes straight into the left ring neighbour's ghost cells, then wait for mine
+            ProfScope ps(*this, PF_HALO);
+            ++in_epoch;
+            const int par = (int)(in_epoch & 1u);
+            const size_t M = (size_t)N * N;
+            push_slice_kernel<<<64, 256, 0, st>>>(recon.p, 0, p2p_grin(p2p_left, pe, M, par), 4, 0, (int64_t)M,
+                                                  p2p_flag(p2p_base, 5), p2p_flag(p2p_left, 4), in_epoch);
+            wait_flags_kernel<<<1, 1, 0, st>>>(p2p_flag(p2p_base, 4), nullptr, in_epoch, d_err);
+            launches += 2;
+            hn = p2p_grin(p2p_base, pe, M, par);
+        } else if (nranks > 1) { exchange(recon.p, 0, (rank - 1 + nranks) % nranks, ghost(0), (rank + 1) % nranks, ghost(1), 4, 0); hn = ghost(1); }
         tv_value_async(recon.p, 0, hn, 4);
         if (!scratch.ok()) scratch.alloc(n);
         dim3 grid((N + TV_KSEG - 1) / TV_KSEG, (N + TV_WARPS - 1) / TV_WARPS, nxb);
@@ -625,6 +750,7 @@ public:
         FgpParams p;
         p.in = recon.p; p.lambda = lambda; p.multip = 1.0f / (26.0f * lambda); p.d = dims();
         p.hl_P1 = p.hr_in = p.hr_P1 = p.hr_P2 = p.hr_P3 = nullptr;
+        p.compact = 0; p.pitch = 0; p.rm_gl1 = p.rm_gr1 = p.rm_gr2 = p.rm_gr3 = nullptr; p.rm_flagR = p.rm_flagL = nullptr; p.cnt = nullptr; p.epoch = 0;
         const bool has_left = nranks > 1 && rank > 0, has_right = nranks > 1 && rank < nranks - 1;
         if (has_right) p.hr_in = hn;
         int cur = 0;   // P[cur*3 ..] holds the current dual variable
@@ -632,7 +758,17 @@ public:
             const bool first = (it == 0), last = (it == iter - 1);
             if (!first) {
                 p.P1 = P[cur * 3 + 0].p; p.P2 = P[cur * 3 + 1].p; p.P3 = P[cur * 3 + 2].p;
-                if (nranks > 1) {
+                if (p2p) {
+                    // the neighbours' previous sweep wrote their boundary slices straight into my planes
+                    // (peer memory over NVLink) and published fgp_epoch: wait for it, then read parity fgp_epoch&1
+                    ProfScope ps(*this, PF_HALO);
+                    const int par = (int)(fgp_epoch & 1u);
+                    wait_flags_kernel<<<1, 1, 0, st>>>(has_left ? p2p_flag(p2p_base, 0) : nullptr, has_right ? p2p_flag(p2p_base, 1) : nullptr, fgp_epoch, d_err);
+                    ++launches;
+                    p.compact = 1; p.pitch = p2p_pitch;
+                    p.hl_P1 = has_left ? p2p_plane(p2p_base, pe, 0, par) : nullptr;
+                    if (has_right) { p.hr_P1 = p2p_plane(p2p_base, pe, 1, par); p.hr_P2 = p2p_plane(p2p_base, pe, 2, par); p.hr_P3 = p2p_plane(p2p_base, pe, 3, par); }
+                } else if (nranks > 1) {
                     // one gather launch + one NCCL group per sweep, in the ghost-cell layout the kernel's TMA boxes read:
                     //   P1 of my last slice -> right neighbour (its x-1, element 3)       ghost 2 -> its ghost 3
                     //   P1,P2,P3 of my first slice -> left neighbour (its x+1, element 0) ghosts 4,5,6 -> its ghosts 7,8,9
@@ -668,6 +804,17 @@ public:
             } else {
                 const int nxt = first ? 0 : 1 - cur;
                 p.Q1 = P[nxt * 3 + 0].p; p.Q2 = P[nxt * 3 + 1].p; p.Q3 = P[nxt * 3 + 2].p;
+                if (p2p) {
+                    // this sweep's boundary slices go to the neighbours' planes of parity (fgp_epoch+1)&1
+                    ++fgp_epoch;
+                    const int par = (int)(fgp_epoch & 1u);
+                    p.pitch = p2p_pitch; p.epoch = fgp_epoch;
+                    p.cnt = p2p_flag(p2p_base, 2);
+                    p.rm_gl1 = has_right ? p2p_plane(p2p_right, pe, 0, par) : nullptr;
+                    p.rm_flagR = has_right ? p2p_flag(p2p_right, 0) : nullptr;
+                    if (has_left) { p.rm_gr1 = p2p_plane(p2p_left, pe, 1, par); p.rm_gr2 = p2p_plane(p2p_left, pe, 2, par); p.rm_gr3 = p2p_plane(p2p_left, pe, 3, par); }
+                    p.rm_flagL = has_left ? p2p_flag(p2p_left, 1) : nullptr;
+                }
                 ProfScope ps(*this, first ? PF_FGP_FIRST : PF_FGP_SWEEP);
                 if (fgp_tiled) fgp_launch(first ? FGP_FIRST : FGP_SWEEP, p, nullptr);
                 else {
@@ -680,7 +827,15 @@ public:
             TTV_LAUNCH_CHECK();
         }
         std::swap(recon.p, scratch.p);   // the volume is replaced by the last D (tv_fgp.cu:272)
-        return (float)fetch_red(0);
+        const float tv0 = (float)fetch_red(0);
+        if (p2p) {
+            int err[4] = {0, 0, 0, 0};
+            TTV_CUDA(cudaMemcpyAsync(err, d_err, sizeof err, cudaMemcpyDeviceToHost, st)); sync();
+            if (err[0]) throw CudaError("tv_fgp: timed out waiting for a neighbouring rank's halo epoch (peer-memory hand-off): rank " + std::to_string(rank) +
+                                        " side " + std::to_string(err[1]) + " flag " + std::to_string(err[2]) + " wanted " + std::to_string(err[3]) +
+                                        " in_epoch " + std::to_string(in_epoch) + " fgp_epoch " + std::to_string(fgp_epoch));
+        }
+        return tv0;
     }
 
     // cuda_tv_gd_3D, tv_gd.cu:141-218.  Returns TV of the input.

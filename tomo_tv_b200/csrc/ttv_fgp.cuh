@@ -38,7 +38,9 @@ constexpr uint32_t FGP_MAIN_ARR = FGP_RJ * FGP_CW * 128u;                 // byt
 constexpr uint32_t FGP_HALO_BOX = FGP_RJ * FGP_CW * 16u;                  // bytes of one 16-byte-cell box
 constexpr uint32_t FGP_HALO_ARR = (FGP_HALO_BOX + 127u) / 128u * 128u;    // padded to the TMA alignment
 constexpr uint32_t FGP_STAGE = 4 * FGP_MAIN_ARR + 5 * FGP_HALO_ARR;
-constexpr size_t FGP_SMEM = (size_t)FGP_NS * FGP_STAGE + (size_t)FGP_DR * 32 * 128 + (size_t)FGP_DR * 32 * 4 + 128 + FGP_NS * 8;
+constexpr int FGP_PB = FGP_CW + 3;                 // compact ghost-plane box: 36 floats = 144 B per row
+constexpr uint32_t FGP_PLANE_BOX = FGP_RJ * FGP_PB * 4u;
+constexpr size_t FGP_SMEM = (size_t)FGP_NS * FGP_STAGE + (size_t)FGP_DR * 32 * 128 + (size_t)FGP_DR * 32 * 4 + 128 + 2048 + FGP_NS * 8;
 
 enum FgpMode { FGP_SWEEP = 0, FGP_FIRST = 1, FGP_FINAL = 2 };
 
@@ -55,7 +57,8 @@ fgp_tile_kernel(const __grid_constant__ FgpMaps tm, const FgpParams p, float* __
     const uint32_t s_stage = smem_u32(smem_raw);
     const uint32_t s_D = s_stage + FGP_NS * FGP_STAGE;             // [DR][32 cells][32 lanes]
     const uint32_t s_X = s_D + FGP_DR * 32 * 128;                  // [DR][32 cells] D of slice x+1 (+128 B pad)
-    uint64_t* full = reinterpret_cast<uint64_t*>(smem_raw + (size_t)FGP_NS * FGP_STAGE + (size_t)FGP_DR * 32 * 128 + (size_t)FGP_DR * 32 * 4 + 128);
+    const uint32_t s_E = s_X + FGP_DR * 32 * 4 + 128;              // [2 parities][4 planes][2 rows][32 cells] boundary-slice values for the neighbours
+    uint64_t* full = reinterpret_cast<uint64_t*>(smem_raw + (size_t)FGP_NS * FGP_STAGE + (size_t)FGP_DR * 32 * 128 + (size_t)FGP_DR * 32 * 4 + 128 + 2048);
 
     const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
     const int N = p.d.N;
@@ -69,6 +72,15 @@ fgp_tile_kernel(const __grid_constant__ FgpMaps tm, const FgpParams p, float* __
     const bool has_xp = !lastblk || (p.hr_in != nullptr);     // a slice x+1 exists for the block's edge lane
     const bool has_xm = xb > 0 || (p.hl_P1 != nullptr);       // a slice x-1 exists for lane 0
     const float lambda = p.lambda, multip = p.multip;
+    // sharded volume: ghost layout of the P slices (16-byte cells from NCCL, or compact planes written by the peer)
+    const bool cR = lastblk && p.compact, cL = (xb == 0) && p.compact;
+    // (a TMA box must start 16-byte aligned in the innermost dimension: the compact box starts at ka <= k0-1)
+    const int ka = (k0 - 1) & ~3;
+    const uint32_t rsR = cR ? FGP_PB * 4u : FGP_CW * 16u, csR = cR ? 4u : 16u;             // x+1 side: row / cell stride
+    const uint32_t aoR = cR ? (uint32_t)(k0 - 1 - ka) * 4u : 0u;
+    const uint32_t rsL = cL ? FGP_PB * 4u : FGP_CW * 16u, csL = cL ? 4u : 16u, eoL = cL ? (uint32_t)(k0 - 1 - ka) * 4u : 12u;
+    const bool send_r = (MODE != FGP_FINAL) && lastblk && (p.rm_gl1 != nullptr);           // my last slice -> right neighbour
+    const bool send_l = (MODE != FGP_FINAL) && (xb == 0) && (p.rm_gr1 != nullptr);         // my first slice -> left neighbour
 
     if (tid == 0) {
         for (int s = 0; s < FGP_NS; ++s) mbar_init(&full[s], 1);
@@ -106,18 +118,43 @@ fgp_tile_kernel(const __grid_constant__ FgpMaps tm, const FgpParams p, float* __
                         tma_load_4d(sb + 4 * FGP_MAIN_ARR + (size_t)a * FGP_HALO_ARR, m, &full[buf], 0, k0 - 1, row, xb + 1);
                     } else {
                         const CUtensorMap* m = a == 0 ? &tm.grin : a == 1 ? &tm.gr1 : a == 2 ? &tm.gr2 : &tm.gr3;
-                        tma_load_4d(sb + 4 * FGP_MAIN_ARR + (size_t)a * FGP_HALO_ARR, m, &full[buf], 0, k0 - 1, row, 0);
+                        if (a > 0 && cR) tma_load_4d(sb + 4 * FGP_MAIN_ARR + (size_t)a * FGP_HALO_ARR, m, &full[buf], ka, row, 0, 0);
+                        else tma_load_4d(sb + 4 * FGP_MAIN_ARR + (size_t)a * FGP_HALO_ARR, m, &full[buf], 0, k0 - 1, row, 0);
                     }
                 } else if (xb > 0) {
                     tma_load_4d(sb + 4 * FGP_MAIN_ARR + 4 * FGP_HALO_ARR, &tm.p1h, &full[buf], 28, k0 - 1, row, xb - 1);
+                } else if (cL) {
+                    tma_load_4d(sb + 4 * FGP_MAIN_ARR + 4 * FGP_HALO_ARR, &tm.gl1, &full[buf], ka, row, 0, 0);
                 } else {
                     tma_load_4d(sb + 4 * FGP_MAIN_ARR + 4 * FGP_HALO_ARR, &tm.gl1, &full[buf], 0, k0 - 1, row, 0);
                 }
             }
             const unsigned m = __ballot_sync(0xffffffffu, want);
             if (lane == 0) {
-                const uint32_t bytes = (uint32_t)__popc(m & 0xFu) * FGP_MAIN_ARR + (uint32_t)__popc(m & 0x1F0u) * FGP_HALO_BOX;
+                uint32_t bytes = (uint32_t)__popc(m & 0xFu) * FGP_MAIN_ARR + (uint32_t)__popc(m & 0x10u) * FGP_HALO_BOX;
+                bytes += (uint32_t)__popc(m & 0xE0u) * (cR ? FGP_PLANE_BOX : FGP_HALO_BOX);
+                bytes += (uint32_t)__popc(m & 0x100u) * (cL ? FGP_PLANE_BOX : FGP_HALO_BOX);
                 mbar_arrive_expect_tx(&full[buf], bytes);
+            }
+        };
+        // coalesced store of the boundary-slice values the compute warps left in shared memory for stage s
+        // (rows rowbase-1 and rowbase, 31 cells each) into the neighbours' compact planes
+        auto flush = [&](int s) {
+            const int rowb = ja - 1 + s * FGP_RJ;
+            const int k = k0 + lane;
+            const uint32_t eb = s_E + (uint32_t)(s & 1) * 1024u + (uint32_t)lane * 4u;
+#pragma unroll
+            for (int rq = 0; rq < 2; ++rq) {
+                const int j = rowb - 1 + rq;
+                if (lane < FGP_TK && k < N && j >= ja && j < jb) {
+                    const int64_t o = (int64_t)j * p.pitch + k;
+                    if (send_r) p.rm_gl1[o] = lds32(eb + (uint32_t)(0 * 2 + rq) * 128u);
+                    if (send_l) {
+                        p.rm_gr1[o] = lds32(eb + (uint32_t)(1 * 2 + rq) * 128u);
+                        p.rm_gr2[o] = lds32(eb + (uint32_t)(2 * 2 + rq) * 128u);
+                        p.rm_gr3[o] = lds32(eb + (uint32_t)(3 * 2 + rq) * 128u);
+                    }
+                }
             }
         };
         for (int s = 0; s < FGP_NS - 1; ++s) issue(s);
@@ -134,12 +171,12 @@ fgp_tile_kernel(const __grid_constant__ FgpMaps tm, const FgpParams p, float* __
                 for (int r = 0; r < FGP_RJ; ++r) {
                     const int j = rowbase + r;
                     float D;
-                    const uint32_t hb = sb + 4 * FGP_MAIN_ARR + (uint32_t)(r * FGP_CW + lane + 1) * 16u;
-                    const float inn = lds32(hb);
+                    const float inn = lds32(sb + 4 * FGP_MAIN_ARR + (uint32_t)(r * FGP_CW + lane + 1) * 16u);
                     if (MODE == FGP_FIRST) D = fmaxf(inn, 0.0f);
                     else {
+                        const uint32_t hb = sb + 4 * FGP_MAIN_ARR + (uint32_t)r * rsR + (uint32_t)(lane + 1) * csR + aoR;
                         const float q1 = lds32(hb + FGP_HALO_ARR), q2 = lds32(hb + 2 * FGP_HALO_ARR), q3 = lds32(hb + 3 * FGP_HALO_ARR);
-                        const float v3 = lds32(hb + 3 * FGP_HALO_ARR - 16u);
+                        const float v3 = lds32(hb + 3 * FGP_HALO_ARR - csR);
                         const float v1 = lds32(sb + FGP_MAIN_ARR + (uint32_t)(r * FGP_CW + lane + 1) * 128u + (uint32_t)edge_lane * 4u);
                         const float sum = ((((q1 + q2) + q3) - v1) - hq2) - v3;
                         D = fmaxf(__fmaf_rn(-lambda, sum, inn), 0.0f);
@@ -149,6 +186,30 @@ fgp_tile_kernel(const __grid_constant__ FgpMaps tm, const FgpParams p, float* __
                 }
             }
             asm volatile("bar.sync 1, %0;" ::"n"(FGP_THREADS) : "memory");
+            if ((send_r || send_l) && it >= 1) flush(it - 1);           // stage it-1's Pn rows are complete
+        }
+        if (send_r || send_l) {
+            asm volatile("bar.sync 1, %0;" ::"n"(FGP_THREADS) : "memory");
+            flush(nst - 1);
+            // every store of this CTA is performed system-wide before the CTA is counted; the last CTA of
+            // each side publishes the epoch on the neighbour (release) -- its wait kernel acquires it
+            __threadfence_system();
+            __syncwarp();
+            if (lane == 0) {
+                const unsigned expect = gridDim.y * gridDim.z;
+                if (send_r) {
+                    if (atomicAdd(&p.cnt[0], 1u) == expect - 1) {
+                        p.cnt[0] = 0; __threadfence_system();
+                        asm volatile("st.release.sys.global.u32 [%0], %1;" ::"l"(p.rm_flagR), "r"(p.epoch) : "memory");
+                    }
+                }
+                if (send_l) {
+                    if (atomicAdd(&p.cnt[1], 1u) == expect - 1) {
+                        p.cnt[1] = 0; __threadfence_system();
+                        asm volatile("st.release.sys.global.u32 [%0], %1;" ::"l"(p.rm_flagL), "r"(p.epoch) : "memory");
+                    }
+                }
+            }
         }
         return;
     }
@@ -192,7 +253,7 @@ fgp_tile_kernel(const __grid_constant__ FgpMaps tm, const FgpParams p, float* __
                     const float v3 = lds32(a + 3 * FGP_MAIN_ARR - 128u);
                     // slice 31 of x-block xb-1 / the left ghost cell (broadcast read; only lane 0 uses it)
                     const float hv = lds32(s_stage + buf * FGP_STAGE + 4 * FGP_MAIN_ARR + 4 * FGP_HALO_ARR
-                                           + (uint32_t)(r * FGP_CW + warp + 1 + h * 16) * 16u + 12u);
+                                           + (uint32_t)r * rsL + (uint32_t)(warp + 1 + h * 16) * csL + eoL);
                     float v1 = __shfl_up_sync(0xffffffffu, p1, 1);
                     if (lane == 0) v1 = has_xm ? hv : 0.0f;
                     const float v2 = (r == 0) ? cP2[h] : P2[h][0];
@@ -250,6 +311,11 @@ fgp_tile_kernel(const __grid_constant__ FgpMaps tm, const FgpParams p, float* __
                         const int64_t o = orow + rq * rstride + h * 512;
                         p.Q1[o] = q1; p.Q2[o] = q2; p.Q3[o] = q3;
                     }
+                    if (send_r || send_l) {
+                        const uint32_t eb = s_E + (uint32_t)(it & 1) * 1024u + (uint32_t)rq * 128u + (uint32_t)(warp + h * 16) * 4u;
+                        if (send_r && lane == edge_lane) sts32(eb, q1);
+                        if (send_l && lane == 0) { sts32(eb + 256u, q1); sts32(eb + 512u, q2); sts32(eb + 768u, q3); }
+                    }
                 }
             }
 #pragma unroll
@@ -261,6 +327,7 @@ fgp_tile_kernel(const __grid_constant__ FgpMaps tm, const FgpParams p, float* __
         }
         orow += FGP_RJ * rstride;
     }
+    if (send_r || send_l) asm volatile("bar.sync 1, %0;" ::"n"(FGP_THREADS) : "memory");
 }
 
 }  // namespace ttv

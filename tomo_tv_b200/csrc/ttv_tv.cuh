@@ -105,6 +105,15 @@ struct FgpParams {
     const float* hr_in; const float* hr_P1; const float* hr_P2; const float* hr_P3;
     float lambda, multip;
     VolDims d;
+    // peer-memory hand-off of a sharded volume (ttv_fgp.cuh, CUDA IPC): with compact != 0 the P ghosts
+    // hl_P1 / hr_P1..3 are compact planes [N][pitch] that the NEIGHBOUR's sweep kernel wrote into this
+    // GPU's memory, and this launch writes its own boundary slices into the neighbours' planes rm_*.
+    int compact, pitch;
+    float* rm_gl1;                                   // on the right neighbour: P1 of my last slice
+    float* rm_gr1; float* rm_gr2; float* rm_gr3;     // on the left neighbour: P1,P2,P3 of my first slice
+    unsigned* rm_flagR; unsigned* rm_flagL;          // epoch flags on the right / left neighbour
+    unsigned* cnt;                                   // local CTA counters [2] (right, left)
+    unsigned epoch;
 };
 
 template <bool FIRST>

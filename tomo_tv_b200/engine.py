@@ -242,6 +242,34 @@ class tomoengine:
         buf = (C.c_char * 128).from_buffer_copy(uid)
         check(lib().ttv_comm_init(self._h, buf, int(rank), int(nranks)))
 
+    def p2p_export(self):
+        buf = (C.c_char * 64)()
+        check(lib().ttv_p2p_export(self._h, buf))
+        return bytes(buf)
+
+    def p2p_attach(self, left, right):
+        l = None if left is None else (C.c_char * 64).from_buffer_copy(left)
+        r = None if right is None else (C.c_char * 64).from_buffer_copy(right)
+        check(lib().ttv_p2p_attach(self._h, l, r))
+
+    def p2p_attach_local(self, left, right):
+        check(lib().ttv_p2p_attach_local(self._h, None if left is None else left._h, None if right is None else right._h))
+
+    def set_rank(self, rank, nranks):
+        check(lib().ttv_set_rank(self._h, int(rank), int(nranks)))
+
+    def setup_sharding(self, dist, rank, world, p2p=True):
+        """NCCL communicator + (optionally) CUDA-IPC peer buffers, using an initialised
+        torch.distributed process group for the rendezvous."""
+        uid = [tomoengine.nccl_unique_id() if rank == 0 else None]
+        dist.broadcast_object_list(uid, src=0)
+        self.comm_init(uid[0], rank, world)
+        if p2p and world > 1:
+            handles = [None] * world
+            dist.all_gather_object(handles, self.p2p_export())
+            # ring neighbours (the periodic TV value needs rank 0 <-> last); the FGP chain ignores the wrap-around
+            self.p2p_attach(handles[(rank - 1) % world], handles[(rank + 1) % world])
+
     # ---- measurement / test hooks (not part of the reference API) -------------------------------
     def sync(self):
         check(lib().ttv_sync(self._h))
