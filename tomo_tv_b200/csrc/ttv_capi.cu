@@ -366,7 +366,8 @@ int ttv_time_kernel(ttv_handle h, const char* name, int reps, int arg_i, float a
         else if (nm == "fgp_sweep") e.fgp_launch(FGP_SWEEP, fp, nullptr);
         else if (nm == "fgp_first") e.fgp_launch(FGP_FIRST, fp, nullptr);
         else if (nm == "fgp_final") e.fgp_launch(FGP_FINAL, fp, e.scratch.p);
-        else if (nm == "tv") { tv_value_kernel<<<(unsigned)((rows + 7) / 8), 256, 0, e.st>>>(e.recon.p, e.dims(), nullptr, 1, e.d_red); ++e.launches; }
+        else if (nm == "tv_v1") { tv_value_kernel<<<(unsigned)((rows + 7) / 8), 256, 0, e.st>>>(e.recon.p, e.dims(), nullptr, 1, e.d_red); ++e.launches; }
+        else if (nm == "tv") { tv_value_tiled_kernel<<<dim3(gsw.x, (e.N + 7) / 8, e.nxb), 256, 0, e.st>>>(e.recon.p, e.dims(), nullptr, 1, e.d_red); ++e.launches; }
         else if (nm == "momentum") { momentum_kernel<<<ew_blocks(n / 4), 256, 0, e.st>>>(reinterpret_cast<float4*>(e.scratch.p), reinterpret_cast<float4*>(e.yk.p), reinterpret_cast<float4*>(e.recon_old.p), 0.5f, n / 4); ++e.launches; }
         else if (nm == "tvgd_grad") { tvgd_gradient_kernel<<<dim3(gsw.x, (e.N + 7) / 8, e.nxb), 256, 0, e.st>>>(gp); ++e.launches; }
         else if (nm == "tvgd_update") { tvgd_update_kernel<<<ew_blocks(n / 4), 256, 0, e.st>>>(e.yk.p, e.scratch.p, e.d_red + 1, 0.f, 0, n / 4); ++e.launches; }

@@ -238,6 +238,8 @@ public:
     DBuf stage;                      // host I/O staging (reference layout, one x-block)
     DBuf planes;                     // halo planes
     double* d_red = nullptr;         // reduction slots
+    double* h_red = nullptr;         // pinned mirror: [0..15] reduction slots, then 4 ints of d_err
+    cudaEvent_t ev_red = nullptr;
     int* d_imax = nullptr;
 
     bool momentum = false, weights_ready = false, sart_ready = false, fp_ready = false, kl_ready = false;
@@ -311,12 +313,18 @@ public:
         nxb = (nx + 31) / 32;
         recon.alloc(vol_elems());
         TTV_CUDA(cudaMalloc(&d_red, 16 * sizeof(double)));
+        TTV_CUDA(cudaMallocHost(&h_red, 18 * sizeof(double)));
+        std::memset(h_red, 0, 18 * sizeof(double));
+        TTV_CUDA(cudaEventCreateWithFlags(&ev_red, cudaEventDisableTiming));
         TTV_CUDA(cudaMalloc(&d_imax, sizeof(int)));
         size_t stage_elems = (size_t)32 * std::max<size_t>((size_t)N * N, 1);
         stage.alloc(stage_elems);
-        TTV_CUDA(cudaFuncSetAttribute(fgp_tile_kernel<FGP_SWEEP>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)FGP_SMEM));
-        TTV_CUDA(cudaFuncSetAttribute(fgp_tile_kernel<FGP_FIRST>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)FGP_SMEM));
-        TTV_CUDA(cudaFuncSetAttribute(fgp_tile_kernel<FGP_FINAL>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)FGP_SMEM));
+        TTV_CUDA(cudaFuncSetAttribute(fgp_tile_kernel<FGP_SWEEP, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)FGP_SMEM));
+        TTV_CUDA(cudaFuncSetAttribute(fgp_tile_kernel<FGP_FIRST, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)FGP_SMEM));
+        TTV_CUDA(cudaFuncSetAttribute(fgp_tile_kernel<FGP_FINAL, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)FGP_SMEM));
+        TTV_CUDA(cudaFuncSetAttribute(fgp_tile_kernel<FGP_SWEEP, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)FGP_SMEM));
+        TTV_CUDA(cudaFuncSetAttribute(fgp_tile_kernel<FGP_FIRST, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)FGP_SMEM));
+        TTV_CUDA(cudaFuncSetAttribute(fgp_tile_kernel<FGP_FINAL, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)FGP_SMEM));
         if (nang > 0) set_angles(ang, nang);
     }
     ~Engine() {
@@ -328,6 +336,8 @@ public:
         for (DBuf* d : {&recon, &yk, &recon_old, &temp, &original, &b, &g, &r, &scratch, &R, &C, &stage, &planes}) d->release();
         for (auto& d : P) d.release();
         cudaFree(d_win0); cudaFree(d_fpang); cudaFree(d_fpgrp); cudaFree(d_theta); cudaFree(d_red); cudaFree(d_imax);
+        if (h_red) cudaFreeHost(h_red);
+        if (ev_red) cudaEventDestroy(ev_red);
         for (auto& r : prof_pending) { cudaEventDestroy(r.a); cudaEventDestroy(r.b); }
         if (tm_a) { cudaEventDestroy(tm_a); cudaEventDestroy(tm_b); }
         if (st) cudaStreamDestroy(st);
@@ -663,7 +673,9 @@ public:
         const int64_t rows = (int64_t)nxb * N;
         {
             ProfScope ps(*this, PF_TV);
-            tv_value_kernel<<<(unsigned)((rows + 7) / 8), 256, 0, st>>>(v, dims(), hn, hs, d_red + slot); ++launches;
+            (void)rows;
+            dim3 g((N + TV_KSEG - 1) / TV_KSEG, (N + 7) / 8, nxb);
+            tv_value_tiled_kernel<<<g, 256, 0, st>>>(v, dims(), hn, hs, d_red + slot); ++launches;
         }
         TTV_LAUNCH_CHECK();
         if (nranks > 1 && comm) {   // (same-process slab engines without a communicator return their partial sum)
@@ -676,10 +688,40 @@ public:
         return v;
     }
     double tv_value(const float* v) { tv_value_async(v, 0); return fetch_red(0); }
+    // early scalar return: the D2H copy of slot (and of the hand-off error word) is queued right after the
+    // reduction, so a caller can queue the rest of its kernels and then wait for this event only -- the host
+    // returns while the sweeps still run and the next API call is already being enqueued behind them
+    void red_post(int slot) {
+        TTV_CUDA(cudaMemcpyAsync(h_red + slot, d_red + slot, sizeof(double), cudaMemcpyDeviceToHost, st));
+        if (d_err) TTV_CUDA(cudaMemcpyAsync(h_red + 16, d_err, 4 * sizeof(int), cudaMemcpyDeviceToHost, st));
+        TTV_CUDA(cudaEventRecord(ev_red, st));
+    }
+    double red_wait(int slot) {
+        TTV_CUDA(cudaEventSynchronize(ev_red));
+        const int* err = reinterpret_cast<const int*>(h_red + 16);
+        if (err[0]) throw CudaError("timed out waiting for a neighbouring rank's halo epoch (peer-memory hand-off): rank " + std::to_string(rank) +
+                                    " side " + std::to_string(err[1]) + " flag " + std::to_string(err[2]) + " wanted " + std::to_string(err[3]));
+        return h_red[slot];
+    }
 
     // one tiled FGP launch (ttv_fgp.cuh); mode FGP_FIRST ignores P, FGP_FINAL writes D to `out`
     bool fgp_tiled = true;
-    int fgp_seg() const { return N >= 64 ? 64 : ((N + 1) & ~1); }
+    // rows per j-segment: trade the 2 redundant rows per segment against whole waves of CTAs on the SMs
+    int sm_count = 0;
+    int fgp_seg() {
+        if (N < 48) return (N + 1) & ~1;
+        if (!sm_count) { cudaDeviceProp pr; TTV_CUDA(cudaGetDeviceProperties(&pr, device)); sm_count = pr.multiProcessorCount; }
+        const int kt = (N + FGP_TK - 1) / FGP_TK;
+        if ((double)nxb * kt * ((N + 63) / 64) >= 6.0 * sm_count) return 64;       // many waves: the tail does not matter
+        int best = 64; double beff = -1.0;
+        for (int seg = 24; seg <= 128; seg += 2) {
+            const int z = (N + seg - 1) / seg;
+            const double waves = (double)nxb * kt * z / sm_count;
+            const double eff = waves / std::ceil(waves) * ((double)N / ((double)z * (seg + 2)));
+            if (eff > beff + 1e-9) { beff = eff; best = seg; }
+        }
+        return best;
+    }
     void fgp_launch(int mode, const FgpParams& p, float* out) {
         FgpMaps tm;
         tm.in = make_tmap(p.in, N, N, nxb, FGP_CW, FGP_RJ);
@@ -706,9 +748,16 @@ public:
         }
         const int seg = fgp_seg();
         dim3 grid(nxb, (N + FGP_TK - 1) / FGP_TK, (N + seg - 1) / seg);
-        if (mode == FGP_FIRST) fgp_tile_kernel<FGP_FIRST><<<grid, FGP_THREADS, FGP_SMEM, st>>>(tm, p, out, seg);
-        else if (mode == FGP_FINAL) fgp_tile_kernel<FGP_FINAL><<<grid, FGP_THREADS, FGP_SMEM, st>>>(tm, p, out, seg);
-        else fgp_tile_kernel<FGP_SWEEP><<<grid, FGP_THREADS, FGP_SMEM, st>>>(tm, p, out, seg);
+        const bool shard = p.hl_P1 || p.hr_in || p.rm_gl1 || p.rm_gr1;
+        if (shard) {
+            if (mode == FGP_FIRST) fgp_tile_kernel<FGP_FIRST, true><<<grid, FGP_THREADS, FGP_SMEM, st>>>(tm, p, out, seg);
+            else if (mode == FGP_FINAL) fgp_tile_kernel<FGP_FINAL, true><<<grid, FGP_THREADS, FGP_SMEM, st>>>(tm, p, out, seg);
+            else fgp_tile_kernel<FGP_SWEEP, true><<<grid, FGP_THREADS, FGP_SMEM, st>>>(tm, p, out, seg);
+        } else {
+            if (mode == FGP_FIRST) fgp_tile_kernel<FGP_FIRST, false><<<grid, FGP_THREADS, FGP_SMEM, st>>>(tm, p, out, seg);
+            else if (mode == FGP_FINAL) fgp_tile_kernel<FGP_FINAL, false><<<grid, FGP_THREADS, FGP_SMEM, st>>>(tm, p, out, seg);
+            else fgp_tile_kernel<FGP_SWEEP, false><<<grid, FGP_THREADS, FGP_SMEM, st>>>(tm, p, out, seg);
+        }
         ++launches;
     }
 
@@ -738,13 +787,14 @@ public:
             hn = p2p_grin(p2p_base, pe, M, par);
         } else if (nranks > 1) { exchange(recon.p, 0, (rank - 1 + nranks) % nranks, ghost(0), (rank + 1) % nranks, ghost(1), 4, 0); hn = ghost(1); }
         tv_value_async(recon.p, 0, hn, 4);
+        red_post(0);
         if (!scratch.ok()) scratch.alloc(n);
         dim3 grid((N + TV_KSEG - 1) / TV_KSEG, (N + TV_WARPS - 1) / TV_WARPS, nxb);
         if (iter <= 0) {
             const int64_t rows = (int64_t)nxb * N;
             tv_map_kernel<<<(unsigned)((rows + 7) / 8), 256, 0, st>>>(recon.p, scratch.p, dims(), hn, 4); ++launches;
             std::swap(recon.p, scratch.p);
-            return (float)fetch_red(0);
+            return (float)red_wait(0);
         }
         for (int i = 0; i < 6; ++i) if (!P[i].ok() && iter > 1) P[i].alloc(n);
         FgpParams p;
@@ -827,14 +877,7 @@ public:
             TTV_LAUNCH_CHECK();
         }
         std::swap(recon.p, scratch.p);   // the volume is replaced by the last D (tv_fgp.cu:272)
-        const float tv0 = (float)fetch_red(0);
-        if (p2p) {
-            int err[4] = {0, 0, 0, 0};
-            TTV_CUDA(cudaMemcpyAsync(err, d_err, sizeof err, cudaMemcpyDeviceToHost, st)); sync();
-            if (err[0]) throw CudaError("tv_fgp: timed out waiting for a neighbouring rank's halo epoch (peer-memory hand-off): rank " + std::to_string(rank) +
-                                        " side " + std::to_string(err[1]) + " flag " + std::to_string(err[2]) + " wanted " + std::to_string(err[3]) +
-                                        " in_epoch " + std::to_string(in_epoch) + " fgp_epoch " + std::to_string(fgp_epoch));
-        }
+        const float tv0 = (float)red_wait(0);
         return tv0;
     }
 
@@ -842,8 +885,9 @@ public:
     float tv_gd(int ng, float dPOCS) {
         use();
         const size_t n = vol_elems();
-        tv_value_async(recon.p, 0);
         if (!scratch.ok()) scratch.alloc(n);
+        tv_value_async(recon.p, 0);
+        red_post(0);
         dim3 grid((N + TV_KSEG - 1) / TV_KSEG, (N + 7) / 8, nxb);
         for (int it = 0; it < ng; ++it) {
             GdParams p; p.x = recon.p; p.g = scratch.p; p.hm = p.hp = nullptr; p.sumsq = d_red + 1; p.d = dims();
@@ -882,7 +926,7 @@ public:
             TTV_LAUNCH_CHECK();
         }
         if (ng <= 0) { ew_kernel<EW_POS><<<ew_blocks(n / 4), 256, 0, st>>>(reinterpret_cast<float4*>(recon.p), 0.f, n / 4); ++launches; }
-        return (float)fetch_red(0);
+        return (float)red_wait(0);
     }
 
     template <int OP> double reduce(const float* a, const float* bb, size_t n) {

@@ -49,7 +49,8 @@ enum FgpMode { FGP_SWEEP = 0, FGP_FIRST = 1, FGP_FINAL = 2 };
 // element 0; gl1: left neighbour's last slice of P1 in element 3).  has_gr / has_gl say whether they exist.
 struct FgpMaps { CUtensorMap in, p1, p2, p3, inh, p1h, p2h, p3h, grin, gr1, gr2, gr3, gl1; };
 
-template <int MODE>
+// SHARD: the volume is a slab of a sharded one (ghost maps, peer stores); compiled out on a single GPU
+template <int MODE, bool SHARD>
 __global__ void __launch_bounds__(FGP_THREADS, 1)
 fgp_tile_kernel(const __grid_constant__ FgpMaps tm, const FgpParams p, float* __restrict__ out, int seg)
 {
@@ -69,18 +70,18 @@ fgp_tile_kernel(const __grid_constant__ FgpMaps tm, const FgpParams p, float* __
     const int nx = p.d.nx;
     const bool lastblk = (xb == p.d.nxb - 1);
     const int edge_lane = lastblk ? ((nx - 1) & 31) : 31;
-    const bool has_xp = !lastblk || (p.hr_in != nullptr);     // a slice x+1 exists for the block's edge lane
-    const bool has_xm = xb > 0 || (p.hl_P1 != nullptr);       // a slice x-1 exists for lane 0
+    const bool has_xp = !lastblk || (SHARD && p.hr_in != nullptr);     // a slice x+1 exists for the block's edge lane
+    const bool has_xm = xb > 0 || (SHARD && p.hl_P1 != nullptr);       // a slice x-1 exists for lane 0
     const float lambda = p.lambda, multip = p.multip;
     // sharded volume: ghost layout of the P slices (16-byte cells from NCCL, or compact planes written by the peer)
-    const bool cR = lastblk && p.compact, cL = (xb == 0) && p.compact;
+    const bool cR = SHARD && lastblk && p.compact, cL = SHARD && (xb == 0) && p.compact;
     // (a TMA box must start 16-byte aligned in the innermost dimension: the compact box starts at ka <= k0-1)
     const int ka = (k0 - 1) & ~3;
     const uint32_t rsR = cR ? FGP_PB * 4u : FGP_CW * 16u, csR = cR ? 4u : 16u;             // x+1 side: row / cell stride
     const uint32_t aoR = cR ? (uint32_t)(k0 - 1 - ka) * 4u : 0u;
     const uint32_t rsL = cL ? FGP_PB * 4u : FGP_CW * 16u, csL = cL ? 4u : 16u, eoL = cL ? (uint32_t)(k0 - 1 - ka) * 4u : 12u;
-    const bool send_r = (MODE != FGP_FINAL) && lastblk && (p.rm_gl1 != nullptr);           // my last slice -> right neighbour
-    const bool send_l = (MODE != FGP_FINAL) && (xb == 0) && (p.rm_gr1 != nullptr);         // my first slice -> left neighbour
+    const bool send_r = SHARD && (MODE != FGP_FINAL) && lastblk && (p.rm_gl1 != nullptr);           // my last slice -> right neighbour
+    const bool send_l = SHARD && (MODE != FGP_FINAL) && (xb == 0) && (p.rm_gr1 != nullptr);         // my first slice -> left neighbour
 
     if (tid == 0) {
         for (int s = 0; s < FGP_NS; ++s) mbar_init(&full[s], 1);

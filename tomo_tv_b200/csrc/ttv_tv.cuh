@@ -223,6 +223,72 @@ __global__ void __launch_bounds__(TV_WARPS * 32) fgp_sweep_kernel(const FgpParam
     }
 }
 
+// TV value, tiled: CTA = one x-block x 8 rows x TV_KSEG cells; a warp marches along k carrying the centre
+// value (its k+1 neighbour becomes the next centre), the j+1 row is an L1/L2 hit from the warp below.
+// Same per-voxel arithmetic as tv_value_kernel (periodic forward differences, tv_gd.cu:27-47).
+__global__ void __launch_bounds__(256) tv_value_tiled_kernel(const float* __restrict__ v, VolDims d, const float* __restrict__ halo_next, int hs, double* out)
+{
+    const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
+    const int N = d.N;
+    const int64_t cpb = (int64_t)N * N;
+    const int j = blockIdx.y * 8 + w;
+    const int xb = blockIdx.z;
+    const int k0 = blockIdx.x * TV_KSEG;
+    float tot = 0.0f;
+    double dtot = 0.0;
+    if (j < N) {
+        const int x = xb * 32 + lane;
+        const bool valid = x < d.nx;
+        const bool lastx = (x == d.nx - 1);
+        const int jp = (j + 1 == N) ? 0 : j + 1;
+        const int kend = min(k0 + TV_KSEG, N);
+        const float* rowc = v + ((int64_t)xb * cpb + (int64_t)j * N) * 32 + lane;
+        const float* rowj = v + ((int64_t)xb * cpb + (int64_t)jp * N) * 32 + lane;
+        // x+1 neighbour of the lane whose successor is not lane+1: next x-block, halo slice, or periodic wrap
+        const float* ep = nullptr; int64_t es = 0;
+        if (valid) {
+            if (lastx) {
+                if (halo_next) { ep = halo_next + (int64_t)j * N * hs; es = hs; }
+                else { ep = v + (int64_t)j * N * 32; es = 32; }
+            } else if (lane == 31) { ep = v + (((int64_t)(xb + 1)) * cpb + (int64_t)j * N) * 32; es = 32; }
+        }
+        float c = rowc[(int64_t)k0 * 32];
+        for (int kb = k0; kb < kend; kb += 8) {
+            // all line loads of 8 cells in flight before any arithmetic
+            float vk[8], vj[8], ve[8];
+#pragma unroll
+            for (int u = 0; u < 8; ++u) {
+                const int k = kb + u;
+                const int kp = (k + 1 >= N) ? 0 : k + 1;
+                vk[u] = (k < kend) ? rowc[(int64_t)kp * 32] : 0.0f;
+                vj[u] = (k < kend) ? rowj[(int64_t)k * 32] : 0.0f;
+                ve[u] = (ep && k < kend) ? ep[(int64_t)k * es] : 0.0f;
+            }
+#pragma unroll
+            for (int u = 0; u < 8; ++u) {
+                const int k = kb + u;
+                float vx = __shfl_down_sync(0xffffffffu, c, 1);
+                if (ep) vx = ve[u];
+                if (k < kend && valid) {
+                    const float dx = c - vx, dy = c - vj[u], dz = c - vk[u];
+                    dtot += (double)sqrtf(1e-6f + dx * dx + dy * dy + dz * dz);
+                }
+                c = vk[u];
+            }
+        }
+    }
+    (void)tot;
+    dtot = warp_sum(dtot);
+    __shared__ double sh[8];
+    if (lane == 0) sh[w] = dtot;
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        double s2 = 0;
+        for (int i = 0; i < 8; ++i) s2 += sh[i];
+        atomicAdd(out, s2);
+    }
+}
+
 // last sweep: only D is needed (tv_fgp.cu:247,272): out = max(0, in - lambda*div P)
 __global__ void __launch_bounds__(256) fgp_final_kernel(const FgpParams p, float* __restrict__ out)
 {
