@@ -114,6 +114,65 @@ int ttv_p2p_attach(ttv_handle h, const void* left_handle64, const void* right_ha
 int ttv_p2p_attach_local(ttv_handle h, ttv_handle left, ttv_handle right);
 int ttv_set_rank(ttv_handle h, int rank, int nranks);
 
+/* --- multi-modal data fusion: one entry point per bound method of the reference's pybind11 class
+ * `multimodal` (/root/reference/tomofusion/chemistry/utils/multimodal.cpp:520-564), same names, argument
+ * meaning and host layouts:
+ *   HAADF tilt series   [Nslice][NprojH*Nray]                 bh[s][a*Nray + d]          (:156)
+ *   chemical tilt series [Nslice][Nel*NprojC*Nray]            bChem[s][e*NprojC*Nray + a*Nray + d]   (:159, :342)
+ *   reconstruction       recon[e][s][y][z] (Matrix4D.cpp:34-36), moved one [Ny][Nz] slice at a time (:495)
+ *   sigma                [3][nnz] float32 rows / cols / vals  (:268-274, chemistry/reconstructor.py:150-153) */
+typedef struct ttv_multimodal* ttv_mm_handle;
+int ttv_mm_create(ttv_mm_handle* out, int nslice, int nray, int nelements, const float* haadf_angles_rad, int nhaadf,
+                  const float* chem_angles_rad, int nchem, int device);                                /* :49-109 */
+int ttv_mm_create_slab(ttv_mm_handle* out, int nslice_local, int nray, int nelements, const float* haadf_angles_rad, int nhaadf,
+                       const float* chem_angles_rad, int nchem, int device, int x_offset, int nslice_global);
+int ttv_mm_destroy(ttv_mm_handle h);
+int ttv_mm_initialize_initial_volume(ttv_mm_handle h);                                           /* :120-121 */
+int ttv_mm_set_haadf_tilt_series(ttv_mm_handle h, const float* bh, int rows, int cols);          /* :156 */
+int ttv_mm_set_chem_tilt_series(ttv_mm_handle h, const float* bchem, int rows, int cols);        /* :159 */
+int ttv_mm_set_measureHaadf(ttv_mm_handle h, int flag);                                          /* :127 */
+int ttv_mm_set_measureChem(ttv_mm_handle h, int flag);                                           /* :133 */
+int ttv_mm_measureHaadf(ttv_mm_handle h, int* flag);                                             /* :124 */
+int ttv_mm_measureChem(ttv_mm_handle h, int* flag);                                              /* :130 */
+int ttv_mm_set_gamma(ttv_mm_handle h, float gamma);                                              /* :145-153 */
+int ttv_mm_gamma(ttv_mm_handle h, float* gamma);                                                 /* :142 */
+int ttv_mm_set_recon(ttv_mm_handle h, const float* slice, int element, int s);                   /* :162 */
+int ttv_mm_get_recon(ttv_mm_handle h, float* out, int element, int s);                           /* :495 */
+int ttv_mm_set_original_volume(ttv_mm_handle h, const float* slice, int element, int s);         /* :165 */
+int ttv_mm_get_gpu_id(ttv_mm_handle h, int* id);                                                 /* :117 */
+int ttv_mm_set_gpu(ttv_mm_handle h, int id);                                                     /* :112-114 */
+int ttv_mm_load_sigma(ttv_mm_handle h, const float* triplets, int nnz);                          /* :268-274 */
+int ttv_mm_initialize_FP(ttv_mm_handle h);                                                       /* :168-171 */
+int ttv_mm_initialize_BP(ttv_mm_handle h);                                                       /* :174-177 */
+int ttv_mm_initialize_SIRT(ttv_mm_handle h);                                                     /* :331-336 */
+int ttv_mm_initialize_SART(ttv_mm_handle h, const char* order);                                  /* :374-382 */
+int ttv_mm_forward_projection(ttv_mm_handle h, const float* slice, float* out);                  /* :180-193 */
+int ttv_mm_estimate_lipschitz(ttv_mm_handle h);                                                  /* :259-265 */
+int ttv_mm_rescale_projections(ttv_mm_handle h);                                                 /* :312-328 */
+int ttv_mm_rescale_tomograms(ttv_mm_handle h, float scale);                                      /* :307-309 */
+int ttv_mm_poisson_ml(ttv_mm_handle h, float lambda_chem, float* cost);                          /* :277-304 */
+int ttv_mm_data_fusion(ttv_mm_handle h, float lambda_haadf, float lambda_chem, int niter, const char* method,
+                       float* cost_haadf, float* cost_chem);                                      /* :452-491 */
+int ttv_mm_sirt_data_fusion(ttv_mm_handle h, float lambda_haadf, float lambda_chem, int niter, float* cost_haadf, float* cost_chem); /* :444-445 */
+int ttv_mm_sart_data_fusion(ttv_mm_handle h, float lambda_haadf, float lambda_chem, float* cost_haadf, float* cost_chem);           /* :448-449 */
+int ttv_mm_chemical_SIRT(ttv_mm_handle h, int niter);                                            /* :364-371 */
+int ttv_mm_chemical_SART(ttv_mm_handle h, int niter);                                            /* :415-423 */
+int ttv_mm_data_distance(ttv_mm_handle h, float* v);                                             /* :207-218 */
+int ttv_mm_tv_gd(ttv_mm_handle h, int ng, float dPOCS, float* tv);                               /* :494 -> chemistry regularizers/tv_gd.cu */
+int ttv_mm_tv_fgp_4D(ttv_mm_handle h, int ng, float lambda, float* tv);                          /* :497 -> chemistry regularizers/tv_fgp.cu:192-281 */
+int ttv_mm_rmse(ttv_mm_handle h, float* per_element);                                            /* :503-506 */
+int ttv_mm_get_haadf_projections(ttv_mm_handle h, float* out);                                   /* :513 */
+int ttv_mm_get_chem_projections(ttv_mm_handle h, float* out);                                    /* :514 */
+int ttv_mm_get_model_projections(ttv_mm_handle h, float* out);                                   /* :512 */
+int ttv_mm_restart_recon(ttv_mm_handle h);                                                       /* :517 */
+/* additions: bulk element volume [Nslice][Ny][Nz], launch counter, stream timer */
+int ttv_mm_get_recon_all(ttv_mm_handle h, float* out, int element);
+int ttv_mm_set_recon_all(ttv_mm_handle h, const float* in, int element);
+int ttv_mm_launch_count(ttv_mm_handle h, long long* n);
+int ttv_mm_timer_start(ttv_mm_handle h);
+int ttv_mm_timer_stop(ttv_mm_handle h, float* ms);
+int ttv_mm_comm_init(ttv_mm_handle h, const void* id128, int rank, int nranks);
+
 /* --- measurement / test hooks (not part of the reference API) ------------------------------- */
 int ttv_sync(ttv_handle h);
 /* device-side __cosf/__sinf of the per-angle FP angle, as the projector evaluates them */

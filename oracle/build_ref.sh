@@ -7,6 +7,7 @@
 # Outputs:
 #   oracle/_ref/libastra.so                      ASTRA fork (thirdparty/astra-toolbox, commit e44162bb)
 #   oracle/_ref/tomoengine<EXT>.so               reference GPU engine   (tomofusion/gpu/utils/tomoengine.cpp)
+#   oracle/_ref/multimodal<EXT>.so               reference fusion engine (tomofusion/chemistry/utils/multimodal.cpp)
 #   oracle/_ref/ctvlib<EXT>.so                   reference CPU engine   (tomofusion/cpu/utils/ctvlib.cpp)
 #
 # The reference's own build system (autotools + Makefiles) is NOT run; this is plain g++/nvcc on
@@ -47,6 +48,20 @@ if [ ! -f "$OUT/tomoengine$EXT" ]; then
       -DASTRA_CUDA -I$A -I$A/include -I$CUDA/include $G/tomoengine.cpp \
       $OBJ/tomo/Matrix3D.o $OBJ/tomo/matrix_ops.o $OBJ/tomo/tv_gd.o $OBJ/tomo/tv_fgp.o \
       -o "$OUT/tomoengine$EXT" -L"$OUT" -lastra -Wl,-rpath,'$ORIGIN' -L$CUDA/lib64 -lcudart
+fi
+
+if [ ! -f "$OUT/multimodal$EXT" ]; then
+  echo "[build_ref] reference fusion engine multimodal"
+  M=$REF/tomofusion/chemistry/utils
+  mkdir -p "$OBJ/chem"
+  for f in container/matrix_ops regularizers/tv_gd regularizers/tv_fgp; do
+    nvcc -w -Xcompiler -fPIC $ARCH -c $M/$f.cu -o $OBJ/chem/$(basename $f).o
+  done
+  g++ -fPIC -O3 -std=c++17 -w -I$REF/thirdparty/eigen -I$M -c $M/container/Matrix4D.cpp -o $OBJ/chem/Matrix4D.o
+  g++ -fPIC -fopenmp -O3 -w -Wno-div-by-zero -shared -std=c++17 $PYB -I$REF/thirdparty/eigen -I$M \
+      -DASTRA_CUDA -I$A -I$A/include -I$CUDA/include $M/multimodal.cpp \
+      $OBJ/chem/Matrix4D.o $OBJ/chem/matrix_ops.o $OBJ/chem/tv_gd.o $OBJ/chem/tv_fgp.o \
+      -o "$OUT/multimodal$EXT" -L"$OUT" -lastra -Wl,-rpath,'$ORIGIN' -L$CUDA/lib64 -lcudart
 fi
 
 if [ ! -f "$OUT/ctvlib$EXT" ]; then

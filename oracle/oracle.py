@@ -272,3 +272,155 @@ class Oracle:
         tgt = self.yk if self.momentum else self.recon
         lib().orc_soft_threshold(tgt.reshape(-1), lam, tgt.size)
         lib().orc_positivity(tgt.reshape(-1), tgt.size)
+
+
+class OracleMM:
+    """CPU mirror of the reference's `multimodal` state machine
+    (/root/reference/tomofusion/chemistry/utils/multimodal.cpp), float32, recon[e][x][y][z].
+    Projector calls go through oracle.c; the Eigen vector arithmetic is restated with numpy float32
+    operations in the same order (one rounding per operation, no contraction)."""
+
+    def __init__(self, ns, nray, nel, haadf_angles, chem_angles, quant=1, trig_h=(None, None), trig_c=(None, None)):
+        self.nx, self.n, self.nel = int(ns), int(nray), int(nel)
+        self.oh = Oracle(ns, nray, haadf_angles, quant, *trig_h)      # HAADF geometry; oh.b = bh, oh.g = g
+        self.oc = Oracle(ns, nray, chem_angles, quant, *trig_c)       # chemical geometry
+        self.nh, self.nc = self.oh.na, self.oc.na
+        self.X = np.zeros((self.nel, self.nx, self.n, self.n), np.float32)
+        self.bc = np.zeros((self.nel, self.nx, self.nc * self.n), np.float32)
+        self.W = None
+        self.gamma = np.float32(1.0)
+        self.eps = np.float32(1e-1)
+        self.measureHaadf = self.measureChem = False
+        self.L_Aps = None
+
+    # multimodal.cpp:156,159
+    def set_haadf_tilt_series(self, bh):
+        self.oh.set_tilt_series(bh)
+
+    def set_chem_tilt_series(self, bchem):
+        b = np.ascontiguousarray(bchem, np.float32).reshape(self.nx, self.nel, self.nc * self.n)
+        self.bc = np.ascontiguousarray(np.transpose(b, (1, 0, 2)))
+
+    def set_gamma(self, g):
+        self.gamma = np.float32(g)
+
+    def set_measureHaadf(self, f):
+        self.measureHaadf = bool(f)
+
+    def set_measureChem(self, f):
+        self.measureChem = bool(f)
+
+    # multimodal.cpp:268-274 with the structure of fusion_helper.py:5-32: entry (p, p + Npix*e) = w
+    def load_sigma(self, trip):
+        t = np.asarray(trip, np.float32)
+        npix = self.n * self.n
+        self.W = np.zeros((self.nel, npix), np.float32)
+        r, c = t[0].astype(np.int64), t[1].astype(np.int64)
+        assert np.all(c % npix == r)
+        self.W[c // npix, r] = t[2]
+        self.W = self.W.reshape(self.nel, 1, self.n, self.n)
+
+    def initialize_FP(self): pass
+    def initialize_BP(self): pass
+
+    def initialize_SIRT(self):
+        self.oh.initialize_SIRT()
+
+    def estimate_lipschitz(self):            # :259-265
+        self.L_Aps = np.float32(self.oc.lipschitz())
+
+    def restart_recon(self):
+        self.X[:] = 0
+
+    def get_recon(self, e, s):
+        return self.X[e, s].copy()
+
+    def _model(self):                        # sigma * x^gamma, row-major sparse product: one rounded product added at a time
+        m = np.zeros((self.nx, self.n, self.n), np.float32)
+        for e in range(self.nel):
+            v = self.X[e] if self.gamma == 1 else np.power(self.X[e], self.gamma, dtype=np.float32)
+            m = m + self.W[e] * v
+        return m
+
+    def _fp(self, o, vol):
+        out = np.zeros((self.nx, o.na * self.n), np.float32)
+        lib().orc_fp3d(np.ascontiguousarray(vol, np.float32), out, self.nx, self.n, o.na, o.geo.p, _ptr(o.geo.cosv), _ptr(o.geo.sinv), o.quant)
+        return out
+
+    def poisson_ml(self, lam):               # :277-304
+        cost = 0.0
+        for e in range(self.nel):
+            x = np.ascontiguousarray(self.X[e])
+            cost += lib().orc_kl3d(x, np.ascontiguousarray(self.bc[e]), self.nx, self.n, self.nc, self.oc.geo.p,
+                                   _ptr(self.oc.geo.cosv), _ptr(self.oc.geo.sinv), lam, self.L_Aps, self.oc.quant)
+            self.X[e] = x
+        return float(cost) if self.measureChem else 0.0
+
+    def rescale_tomograms(self, scale):      # :307-309
+        self.X *= np.float32(scale)
+
+    def rescale_projections(self):           # :312-328
+        self.oh.g = self._fp(self.oh, self._model())
+        b = self.oh.b.reshape(self.nx, self.nh, self.n)
+        g = self.oh.g.reshape(self.nx, self.nh, self.n)
+        for p in range(self.nh):
+            b[:, p, :] = b[:, p, :] / b[:, p, :].max()
+            b[:, p, :] = b[:, p, :] * g[:, p, :].max()
+
+    def sirt_data_fusion(self, lamH, lamC, niter):   # data_fusion("SIRT"), :452-491; fuse :425-441
+        lamH, lamC = np.float32(lamH), np.float32(lamC)
+        m = self._model()
+        self.oh.g = self._fp(self.oh, m)
+        u = m.copy()
+        self.oh._weights()
+        lib().orc_sirt3d(u, self.oh.b, self.oh.R, self.oh.C, self.nx, self.n, self.nh, self.oh.geo.p,
+                         _ptr(self.oh.geo.cosv), _ptr(self.oh.geo.sinv), niter, self.oh.quant)
+        c = np.float32(lamC / self.L_Aps)
+        d = u - m
+        cost = 0.0
+        for e in range(self.nel):
+            x = self.X[e]
+            Ax = self._fp(self.oc, x)
+            b = self.bc[e]
+            cost += float(np.sum((Ax - b * np.log(Ax + self.eps)).astype(np.float64)))
+            ratio = (Ax - b) / (Ax + self.eps)
+            updC = self.oc.back_projection_of(ratio)
+            h = self.W[e] * d
+            if self.gamma != 1:
+                h = (self.gamma * np.power(x, self.gamma - np.float32(1), dtype=np.float32)) * h
+            xn = x - (c * updC - lamH * h)
+            self.X[e] = np.maximum(xn, np.float32(0))
+        costH = float(np.sqrt(lib().orc_sqdist(self.oh.g, self.oh.b, self.oh.g.size))) if self.measureHaadf else 0.0
+        return costH, (cost if self.measureChem else 0.0)
+
+    def data_distance(self):                 # :207-218
+        s = 0.0
+        for e in range(self.nel):
+            g = self._fp(self.oc, self.X[e])
+            s += lib().orc_sqdist(g, np.ascontiguousarray(self.bc[e]), g.size)
+        return float(np.sqrt(s))
+
+    def tv_fgp_4D(self, ng, lam):            # chemistry regularizers/tv_fgp.cu:192-281 (element loop)
+        tv = np.float32(0)
+        for e in range(self.nel):
+            x = np.ascontiguousarray(self.X[e])
+            tv = np.float32(tv + np.float32(lib().orc_tv_fgp(x, ng, lam, self.nx, self.n, self.n)))
+            self.X[e] = x
+        return float(tv)
+
+    def tv_gd(self, ng, dPOCS):
+        tv = np.float32(0)
+        for e in range(self.nel):
+            x = np.ascontiguousarray(self.X[e])
+            tv = np.float32(tv + np.float32(lib().orc_tv_gd(x, ng, dPOCS, self.nx, self.n, self.n)))
+            self.X[e] = x
+        return float(tv)
+
+    def get_haadf_projections(self):
+        return self.oh.b.copy()
+
+    def get_model_projections(self):
+        return self.oh.g.copy()
+
+    def get_chem_projections(self):
+        return np.ascontiguousarray(np.transpose(self.bc, (1, 0, 2)).reshape(self.nx, -1))

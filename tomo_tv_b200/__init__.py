@@ -3,6 +3,8 @@
 Public surface (mirrors the reference, /root/reference/tomofusion):
     TomoGPU                      tomofusion.gpu.reconstructor.TomoGPU
     tomoengine                   tomofusion.gpu.utils.tomoengine (pybind11 class)
+    ChemicalTomo                 tomofusion.chemistry.reconstructor.ChemicalTomo
+    multimodal                   tomofusion.chemistry.utils.multimodal (pybind11 class)
     pytvlib.initialize_algorithm / run / wbp_filters / sart_orders
     determine_gpu_config, device_count      tomofusion/__init__.py
 
@@ -12,6 +14,8 @@ is the only compute path: there is no CPU fallback and no ASTRA dependency.
 from .engine import tomoengine, device_count, NativeError  # noqa: F401
 from . import pytvlib  # noqa: F401
 from .reconstructor import TomoGPU  # noqa: F401
+from .fusion import multimodal  # noqa: F401
+from .chemistry import ChemicalTomo  # noqa: F401
 
 __version__ = "0.1.0"
 

@@ -31,13 +31,19 @@ constexpr size_t BP_SMEM = (size_t)BP_S * BP_STAGE_BYTES + BP_S * BP_TA * sizeof
 
 __constant__ float4 c_bp_angle[BP_MAX_ANGLES];   // {sc, ss, off, scale}
 
-enum BpEpilogue { BP_STORE = 0, BP_SIRT_UPD = 1, BP_STEP_UPD = 2, BP_ADD = 3 };
+enum BpEpilogue { BP_STORE = 0, BP_SIRT_UPD = 1, BP_STEP_UPD = 2, BP_ADD = 3, BP_FUSE_UPD = 4 };
 
 struct BpParams {
     int N, Nd, Na;
     float* vol;            // output / updated volume (x-interleaved)
     const float* C;        // [N][N] pixel weights (SIRT)
     float step;            // BP_STEP_UPD: x = max(x - step*t, 0);  BP_ADD: x += step*t
+    // BP_FUSE_UPD (multi-modal fusion, T/chemistry/utils/multimodal.cpp:425-441,475-481):
+    //   x = max(x - (step*t - lamH * (gamma*x^(gamma-1)) * (W*(U-M))), 0)
+    const float* M = nullptr;   // modelled HAADF volume  sum_e W_e x_e^gamma
+    const float* U = nullptr;   // SIRT-updated HAADF volume
+    const float* W = nullptr;   // [N][N] summation weight of this element
+    float gamma = 1.f, lamH = 0.f;
 };
 
 template <int EPI>
@@ -153,6 +159,18 @@ bp_kernel(const __grid_constant__ CUtensorMap tmS, const BpParams p)
                         const float c = p.step;
                         r = make_float4(fmaxf(__fsub_rn(x.x, __fmul_rn(c, r.x)), 0.f), fmaxf(__fsub_rn(x.y, __fmul_rn(c, r.y)), 0.f),
                                         fmaxf(__fsub_rn(x.z, __fmul_rn(c, r.z)), 0.f), fmaxf(__fsub_rn(x.w, __fmul_rn(c, r.w)), 0.f));
+                    } else if (EPI == BP_FUSE_UPD) {
+                        // same rounding sequence as the reference's Eigen expressions (no contraction on its x86-64 build)
+                        const float4 m = *reinterpret_cast<const float4*>(p.M + o);
+                        const float4 u = *reinterpret_cast<const float4*>(p.U + o);
+                        const float w = p.W[(size_t)Y * N + X];
+                        const float c = p.step, g = p.gamma, lh = p.lamH, gm1 = p.gamma - 1.0f;
+                        auto upd = [&](float xv, float tv, float mv, float uv) -> float {
+                            float h = __fmul_rn(w, __fsub_rn(uv, mv));
+                            if (g != 1.0f) h = __fmul_rn(__fmul_rn(g, powf(xv, gm1)), h);
+                            return fmaxf(__fsub_rn(xv, __fsub_rn(__fmul_rn(c, tv), __fmul_rn(lh, h))), 0.f);
+                        };
+                        r = make_float4(upd(x.x, r.x, m.x, u.x), upd(x.y, r.y, m.y, u.y), upd(x.z, r.z, m.z, u.z), upd(x.w, r.w, m.w, u.w));
                     } else {  // BP_ADD
                         const float c = p.step;
                         r = make_float4(fmaf(c, r.x, x.x), fmaf(c, r.y, x.y), fmaf(c, r.z, x.z), fmaf(c, r.w, x.w));

@@ -390,3 +390,5 @@ int ttv_time_kernel(ttv_handle h, const char* name, int reps, int arg_i, float a
 }
 
 }  // extern "C"
+
+#include "ttv_capi_fusion.cuh"

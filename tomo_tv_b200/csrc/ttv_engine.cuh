@@ -248,7 +248,7 @@ public:
     float L_A = 0.f, L_Aml = 0.f;
 
     // comm
-    Nccl::comm_t comm = nullptr; int rank = 0, nranks = 1;
+    Nccl::comm_t comm = nullptr; int rank = 0, nranks = 1; bool own_comm = true;
     // peer-memory hand-off (CUDA IPC): [256 B flags+counters][8 compact planes gl1[2], gr1[2], gr2[2], gr3[2]]
     float* p2p_base = nullptr; float* p2p_left = nullptr; float* p2p_right = nullptr;
     bool p2p_ready = false; unsigned fgp_epoch = 0; int p2p_pitch = 0;
@@ -332,15 +332,24 @@ public:
         if (p2p_left && !p2p_local) cudaIpcCloseMemHandle(p2p_left);
         if (p2p_right && !p2p_local) cudaIpcCloseMemHandle(p2p_right);
         cudaFree(p2p_base); cudaFree(d_err);
-        if (comm) Nccl::get().CommDestroy(comm);
+        if (comm && own_comm) Nccl::get().CommDestroy(comm);
         for (DBuf* d : {&recon, &yk, &recon_old, &temp, &original, &b, &g, &r, &scratch, &R, &C, &stage, &planes}) d->release();
         for (auto& d : P) d.release();
-        cudaFree(d_win0); cudaFree(d_fpang); cudaFree(d_fpgrp); cudaFree(d_theta); cudaFree(d_red); cudaFree(d_imax);
+        cudaFree(d_win0); cudaFree(d_fpang); cudaFree(d_fpgrp); cudaFree(d_theta); cudaFree(d_red); cudaFree(d_imax); cudaFree(d_bpconst);
+        { ConstOwner& o = const_owner(device); if (o.e == this) { cudaStreamSynchronize(st); o = ConstOwner(); } }
         if (h_red) cudaFreeHost(h_red);
         if (ev_red) cudaEventDestroy(ev_red);
         for (auto& r : prof_pending) { cudaEventDestroy(r.a); cudaEventDestroy(r.b); }
         if (tm_a) { cudaEventDestroy(tm_a); cudaEventDestroy(tm_b); }
-        if (st) cudaStreamDestroy(st);
+        if (st && own_stream) cudaStreamDestroy(st);
+    }
+    // run on another engine's stream (the fusion path drives two geometries as one stream-ordered sequence)
+    bool own_stream = true;
+    void adopt_stream(cudaStream_t s) {
+        sync();
+        { ConstOwner& o = const_owner(device); if (o.e == this) o.st = s; }
+        if (st && own_stream) cudaStreamDestroy(st);
+        st = s; own_stream = false;
     }
 
     size_t vol_elems() const { return (size_t)nxb * N * N * 32; }
@@ -390,8 +399,12 @@ public:
         // BP constants -> __constant__
         std::vector<float4> kb(Na);
         for (int i = 0; i < Na; ++i) kb[i] = make_float4(geom[i].sc, geom[i].ss, geom[i].off, geom[i].scale);
-        TTV_CUDA(cudaMemcpyToSymbolAsync(c_bp_angle, kb.data(), Na * sizeof(float4), 0, cudaMemcpyHostToDevice, st));
+        cudaFree(d_bpconst);
+        TTV_CUDA(cudaMalloc(&d_bpconst, Na * sizeof(float4)));
+        TTV_CUDA(cudaMemcpyAsync(d_bpconst, kb.data(), Na * sizeof(float4), cudaMemcpyHostToDevice, st));
         sync();
+        ++bp_const_epoch;
+        bind_bp_constants();
         build_fp_plan();
         b.alloc(sino_elems()); g.alloc(sino_elems()); r.release();
         size_t stage_elems = (size_t)32 * std::max((size_t)N * N, (size_t)Na * N);
@@ -489,7 +502,12 @@ public:
         set_fp_attrs();
     }
     template <int EPI> void fp_attr() {
-        TTV_CUDA(cudaFuncSetAttribute(fp_kernel<EPI>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)fp_smem));
+        // the attribute is per kernel, not per engine: engines with different plans (HAADF / chemical geometry)
+        // share it, so opt in to the device maximum once instead of this plan's size
+        int optin = 0;
+        TTV_CUDA(cudaDeviceGetAttribute(&optin, cudaDevAttrMaxSharedMemoryPerBlockOptin, device));
+        if ((size_t)optin < fp_smem) throw CudaError("forward-projector plan needs more shared memory than the device offers");
+        TTV_CUDA(cudaFuncSetAttribute(fp_kernel<EPI>, cudaFuncAttributeMaxDynamicSharedMemorySize, optin));
     }
     void set_fp_attrs() {
         fp_attr<FP_STORE>(); fp_attr<FP_SIRT_RES>(); fp_attr<FP_KL>(); fp_attr<FP_STORE_DIST>(); fp_attr<FP_RESID>();
@@ -497,6 +515,20 @@ public:
         TTV_CUDA(cudaFuncSetAttribute(bp_kernel<BP_SIRT_UPD>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)BP_SMEM));
         TTV_CUDA(cudaFuncSetAttribute(bp_kernel<BP_STEP_UPD>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)BP_SMEM));
         TTV_CUDA(cudaFuncSetAttribute(bp_kernel<BP_ADD>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)BP_SMEM));
+        TTV_CUDA(cudaFuncSetAttribute(bp_kernel<BP_FUSE_UPD>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)BP_SMEM));
+    }
+
+    // c_bp_angle is one __constant__ table per device: engines with different angle sets (HAADF / chemical
+    // geometry of the fusion path, several engines in one process) re-bind it, stream-ordered, before they launch
+    float4* d_bpconst = nullptr; unsigned long long bp_const_epoch = 0;
+    struct ConstOwner { const Engine* e = nullptr; unsigned long long epoch = 0; cudaStream_t st = nullptr; };
+    static ConstOwner& const_owner(int dev) { static ConstOwner o[64]; return o[dev & 63]; }
+    void bind_bp_constants() {
+        ConstOwner& o = const_owner(device);
+        if (o.e == this && o.epoch == bp_const_epoch) return;
+        if (o.e && o.st != st) TTV_CUDA(cudaDeviceSynchronize());        // kernels of the previous owner still read the table
+        TTV_CUDA(cudaMemcpyToSymbolAsync(c_bp_angle, d_bpconst, Na * sizeof(float4), 0, cudaMemcpyDeviceToDevice, st));
+        o.e = this; o.epoch = bp_const_epoch; o.st = st;
     }
 
     void need_angles() const { if (Na <= 0) throw CudaError("projection angles were not set (construct with angles or call update_projection_angles)"); }
@@ -520,11 +552,13 @@ public:
         TTV_LAUNCH_CHECK(); ++launches;
     }
     template <int EPI>
-    void bp(const float* sino, float* vol, float step = 0.f, int nblocks = -1) {
+    void bp(const float* sino, float* vol, float step = 0.f, int nblocks = -1, const BpParams* extra = nullptr) {
         need_angles();
         const int zb = nblocks < 0 ? nxb : nblocks;
         CUtensorMap tmS = make_tmap(sino, N, Na, zb, BP_CW, 1);
-        BpParams p; p.N = N; p.Nd = N; p.Na = Na; p.vol = vol; p.C = C.p; p.step = step;
+        bind_bp_constants();
+        BpParams p; if (extra) p = *extra;
+        p.N = N; p.Nd = N; p.Na = Na; p.vol = vol; p.C = C.p; p.step = step;
         const int nt = (N + BP_TILE - 1) / BP_TILE;
         dim3 grid(nt, nt, zb);
         ProfScope ps(*this, PF_BP);
@@ -583,19 +617,24 @@ public:
     }
 
     // one SIRT iteration on `vol`: r = (b - A vol) * R ; vol = max(vol + C * A^T r, 0)   (sirt.cu:237-277)
-    void sirt_step(float* vol) {
+    void sirt_step(float* vol, const float* bmeas = nullptr) {
         if (!r.ok()) r.alloc(sino_elems());
-        fp<FP_SIRT_RES>(vol, r.p, b.p, nullptr);
+        fp<FP_SIRT_RES>(vol, r.p, bmeas ? bmeas : b.p, nullptr);
         bp<BP_SIRT_UPD>(r.p, vol);
     }
 
     // ---------------------------------------------------------------------------------------
     // host I/O in the reference layouts
     // ---------------------------------------------------------------------------------------
-    void upload(DBuf& dst, const float* host, int64_t M) {        // host [nx][M]
+    // host [nx][M]; hstride = host row pitch in floats when the rows are columns of a wider matrix (0 = M)
+    void upload(DBuf& dst, const float* host, int64_t M, int64_t hstride = 0) {
         use();
+        if (stage.n < (size_t)32 * M) stage.alloc((size_t)32 * M);
         for (int xbk = 0; xbk < nxb; ++xbk) {
             const int x0 = xbk * 32, cnt = std::min(32, nx - x0);
+            if (hstride && hstride != M)
+                TTV_CUDA(cudaMemcpy2DAsync(stage.p, M * sizeof(float), host + (size_t)x0 * hstride, hstride * sizeof(float), M * sizeof(float), cnt, cudaMemcpyHostToDevice, st));
+            else
             TTV_CUDA(cudaMemcpyAsync(stage.p, host + (size_t)x0 * M, (size_t)cnt * M * sizeof(float), cudaMemcpyHostToDevice, st));
             dim3 grid((unsigned)((M + 31) / 32), 1);
             pack_kernel<<<grid, 256, 0, st>>>(stage.p, dst.p + (size_t)xbk * M * 32, cnt, M, 0, cnt); ++launches;
@@ -603,13 +642,17 @@ public:
             sync();   // staging buffer is reused
         }
     }
-    void download(const DBuf& src, float* host, int64_t M) {
+    void download(const DBuf& src, float* host, int64_t M, int64_t hstride = 0) {
         use();
+        if (stage.n < (size_t)32 * M) stage.alloc((size_t)32 * M);
         for (int xbk = 0; xbk < nxb; ++xbk) {
             const int x0 = xbk * 32, cnt = std::min(32, nx - x0);
             dim3 grid((unsigned)((M + 31) / 32), 1);
             unpack_kernel<<<grid, 256, 0, st>>>(src.p + (size_t)xbk * M * 32, stage.p, cnt, M, 0, cnt); ++launches;
             TTV_LAUNCH_CHECK();
+            if (hstride && hstride != M)
+                TTV_CUDA(cudaMemcpy2DAsync(host + (size_t)x0 * hstride, hstride * sizeof(float), stage.p, M * sizeof(float), M * sizeof(float), cnt, cudaMemcpyDeviceToHost, st));
+            else
             TTV_CUDA(cudaMemcpyAsync(host + (size_t)x0 * M, stage.p, (size_t)cnt * M * sizeof(float), cudaMemcpyDeviceToHost, st));
             sync();
         }
