@@ -71,7 +71,10 @@ ORC_API void orc_geometry(int nang, int ndet, const float* angles, orc_angle_t* 
         /* getParParameters */
         {
             double ux = detUX, uy = detUY;
-            double t = (ux * rayX + uy * rayY) / ((double)rayX * rayX + (double)rayY * rayY);
+            /* the denominator is float * float + float * float: evaluated in float32 (GeometryUtil2D.cpp:113) */
+            volatile float rx2 = rayX * rayX, ry2 = rayY * rayY;
+            volatile float den = rx2 + ry2;
+            double t = (ux * rayX + uy * rayY) / (double)den;
             ux -= t * rayX; uy -= t * rayY;
             double ang = atan2(uy, ux);
             double norm2 = uy * uy + ux * ux;
@@ -81,11 +84,21 @@ ORC_API void orc_geometry(int nang, int ndet, const float* angles, orc_angle_t* 
         }
         /* par_bp.cu:173-179 */
         {
-            double d = (double)detUX * rayY - (double)detUY * rayX;
+            /* `double d = fDetUX * fRayY - fDetUY * fRayX` etc.: the operands are float members, so products and
+             * differences are rounded to float32 before the promotion (par_bp.cu:174-178; the reference's x86-64
+             * build has no FMA).  Measured: with double products 55 voxels of golden B/kl_bp flip a weight by
+             * 1/256; with float products none do. */
+            volatile float p1 = detUX * rayY, p2 = detUY * rayX;
+            volatile float df = p1 - p2;
+            double d = (double)df;
+            volatile float q1 = detSY * rayX, q2 = detSX * rayY;
+            volatile float nf = q1 - q2;
+            volatile float r1 = rayX * rayX, r2 = rayY * rayY;
+            volatile float rs = r1 + r2;
             g->sc = (float)(rayY / d);
             g->ss = (float)(-rayX / d);
-            g->off = (float)(((double)detSY * rayX - (double)detSX * rayY) / d);
-            g->scale = (float)(sqrt((double)rayX * rayX + (double)rayY * rayY) / fabs(d));
+            g->off = (float)((double)nf / d);
+            g->scale = (float)((double)sqrtf(rs) / fabs(d));
         }
     }
 }
@@ -98,13 +111,24 @@ ORC_API void orc_geometry(int nang, int ndet, const float* angles, orc_angle_t* 
  * In every call site of the hot path the other coordinate is an exact texel centre, so the
  * fetch is one-dimensional.  mode: 0 = Border (zeros outside), 1 = Clamp (edge replicate).
  * ------------------------------------------------------------------------------------------ */
+static inline void tex_coord(float x, int quant, int* i, float* a)
+{
+    if (quant) {
+        /* coordinate -> fixed point with 8 fractional bits, round HALF UP (floor(256x + 0.5)): measured
+         * against the real reference on B200 -- exact ties (e.g. 256*frac = 60.5, 118.5 in
+         * tests/golden B_fp) go up, not to even.  Exact in float32 for |x| < 2^14. */
+        int q = (int)floorf(x * 256.0f + 0.5f) - 128;
+        *i = q >> 8;                    /* arithmetic shift = floor division */
+        *a = (float)(q & 255) * (1.0f / 256.0f);
+    } else {
+        float xb = x - 0.5f, fl = floorf(xb);
+        *i = (int)fl; *a = xb - fl;
+    }
+}
 static inline float tex1d(const float* row, int n, float x, int mode, int quant)
 {
-    float xb = x - 0.5f;
-    float fl = floorf(xb);
-    float a = xb - fl;
-    int i = (int)fl;
-    if (quant) a = rintf(a * 256.0f) * (1.0f / 256.0f);
+    int i; float a;
+    tex_coord(x, quant, &i, &a);
     float v0, v1;
     if (mode == 0) {
         v0 = (i >= 0 && i < n) ? row[i] : 0.0f;
@@ -169,9 +193,8 @@ static void fp_slice(const float* vol, float* sino, int W, int H, int Na, int Nd
                     float acc = 0.0f;
                     for (int cc = c0; cc < c1; ++cc) {
                         /* 1-D fetch down column cc */
-                        float xb = fP - 0.5f, fl = floorf(xb), al = xb - fl;
-                        int j = (int)fl;
-                        if (quant) al = rintf(al * 256.0f) * (1.0f / 256.0f);
+                        int j; float al;
+                        tex_coord(fP, quant, &j, &al);
                         float v0 = (j >= 0 && j < H) ? vol[(size_t)j * W + cc] : 0.0f;
                         float v1 = (j + 1 >= 0 && j + 1 < H) ? vol[(size_t)(j + 1) * W + cc] : 0.0f;
                         acc += (1.0f - al) * v0 + al * v1;

@@ -273,6 +273,136 @@ class Oracle:
         lib().orc_soft_threshold(tgt.reshape(-1), lam, tgt.size)
         lib().orc_positivity(tgt.reshape(-1), tgt.size)
 
+    # -- CGLS: A/cuda/2d/cgls.cu:112-176, one independent run per slice (tomoengine.cpp:214-229) ----
+    def initialize_CGLS(self):
+        pass
+
+    def CGLS(self, niter):
+        f32 = np.float32
+        x = self.recon
+        fp = lambda v: self._fp_of(v)
+        r = (self.b - fp(x)).astype(f32)
+        p = self.back_projection_of(r)
+        gamma = np.sum(p.astype(np.float64) ** 2, axis=(1, 2)).astype(f32)
+        for _ in range(niter):
+            w = fp(p)
+            ww = np.sum(w.astype(np.float64) ** 2, axis=1).astype(f32)
+            alpha = (gamma / ww).astype(f32)
+            x += alpha[:, None, None] * p
+            r = (r - alpha[:, None] * w).astype(f32)
+            z = self.back_projection_of(r)
+            gnew = np.sum(z.astype(np.float64) ** 2, axis=(1, 2)).astype(f32)
+            beta = ((f32(1) / gamma) * gnew).astype(f32)
+            gamma = gnew
+            p = (z + beta[:, None, None] * p).astype(f32)
+        np.maximum(x, 0, out=x)
+
+    def _fp_of(self, vol):
+        out = np.zeros_like(self.b)
+        lib().orc_fp3d(np.ascontiguousarray(vol, np.float32), out, self.nx, self.n, self.na, self.geo.p,
+                       _ptr(self.geo.cosv), _ptr(self.geo.sinv), self.quant)
+        return out
+
+    # -- FBP/WBP: A/cuda/2d/fbp.cu:105-190, fft.cu:251-375, A/src/Filters.cpp:40-420 ---------------
+    def initialize_FBP(self, name):
+        self.fbp_filter = name
+
+    def FBP(self, positivity):
+        n, na = self.n, self.na
+        P = 1
+        while P < 2 * n:
+            P *= 2
+        sino = self.b.reshape(self.nx, na, n)
+        filt = fbp_filter(self.fbp_filter, P)
+        if filt is not None:
+            pad = np.zeros((self.nx, na, P), np.float32)
+            pad[:, :, :n] = sino
+            spec = np.fft.rfft(pad.astype(np.float64), axis=2) * filt.astype(np.float64)
+            sino = (np.fft.irfft(spec, n=P, axis=2)[:, :, :n]).astype(np.float32)     # irfft already divides by P
+        scale = np.float32((np.pi / np.float32(2.0)) / np.float32(na))
+        out = np.zeros_like(self.recon)
+        lib().orc_bp3d(out, np.ascontiguousarray(sino.reshape(self.nx, na * n), np.float32), self.nx, self.n, self.na, self.geo.p, self.quant)
+        self.recon[:] = out * scale
+        if positivity:
+            np.maximum(self.recon, 0, out=self.recon)
+
+
+def fbp_filter(name, P):
+    """astra::genFilter (A/src/Filters.cpp:40-420) with m_fD = 1, m_fParameter = -1 (Filters.h:79);
+    float32 window arithmetic, the ramp spectrum by a double-precision FFT.  None for 'none'."""
+    from scipy.special import j0
+    f32 = np.float32
+    name = name.lower()
+    if name == "none":
+        return None
+    F = P // 2 + 1
+    PI = f32(3.14159265358979323846264338328)
+    h = np.zeros(P, np.float32)
+    i = np.arange(P)
+    j = np.where(2 * i > P, P - i, i).astype(np.float32)
+    odd = (i & 1) == 1
+    fpi = (PI * j[odd]).astype(f32)
+    h[odd] = f32(-1) / (fpi * fpi)
+    h[0] = 0.25
+    filt = (f32(2) * np.real(np.fft.fft(h.astype(np.float64)))[:F].astype(f32)).astype(f32)
+    k = np.arange(F)
+    w = (PI * f32(2) * (k.astype(f32) / f32(P))).astype(f32)
+    n = k.astype(f32)
+    N1 = f32(F - 1)
+
+    def cos4(a0, a1, a2, a3, a4=0.0):
+        base = (PI * n / N1).astype(f32)
+        return (f32(a0) - f32(a1) * np.cos(f32(2) * base) + f32(a2) * np.cos(f32(4) * base) - f32(a3) * np.cos(f32(6) * base)
+                + f32(a4) * np.cos(f32(8) * base)).astype(f32)
+
+    with np.errstate(all="ignore"):
+        if name == "ram-lak":
+            v = np.ones(F, f32)
+        elif name == "shepp-logan":
+            v = np.sin(w / f32(2)) / (w / f32(2))
+        elif name == "cosine":
+            v = np.cos(w / f32(2))
+        elif name == "hamming":
+            v = f32(0.54) + f32(0.46) * np.cos(w)
+        elif name == "hann":
+            v = (f32(1) + np.cos(w)) / f32(2)
+        elif name == "tukey":
+            half = f32(F) / f32(2); en = f32(0.5) * half; den = f32(0.5) * half
+            v = np.where((half - en <= n) & (n <= half + en), f32(1), f32(0.5) * (f32(1) + np.cos(PI * (n - en) / den)))
+        elif name == "lanczos":
+            s = (PI * (f32(2) * n / N1 - f32(1))).astype(f32)
+            v = np.where(np.abs(s) > f32(0.001), np.sin(s.astype(np.float64)) / s.astype(np.float64), 1.0)
+        elif name == "triangular":
+            v = f32(2) / N1 * (N1 / f32(2) - np.abs(n - N1 / f32(2)))
+        elif name == "gaussian":
+            q = (f32(F) - f32(1)) / f32(2); t = (n - q) / (f32(0.4) * q)
+            v = np.exp(f32(-0.5) * t * t)
+        elif name == "barlett-hann":
+            v = f32(0.62) - f32(0.48) * np.abs(n / N1 - f32(0.5)) - f32(0.38) * np.cos(f32(2) * PI * n / N1)
+        elif name == "blackman":
+            al = f32(0.16)
+            v = (f32(1) - al) / f32(2) - f32(0.5) * np.cos(f32(2) * PI * f32(0.5) * n / N1) + (al / f32(2)) * np.cos(f32(4) * PI * f32(0.5) * n / N1)
+        elif name == "nuttall":
+            v = cos4(0.355768, 0.487396, 0.144232, 0.012604)
+        elif name == "blackman-harris":
+            v = cos4(0.35875, 0.48829, 0.14128, 0.01168)
+        elif name == "blackman-nuttall":
+            v = cos4(0.3635819, 0.4891775, 0.1365995, 0.0106411)
+        elif name == "flat-top":
+            v = cos4(1.0, 1.93, 1.29, 0.388, 0.032)
+        elif name == "kaiser":
+            pa = PI * f32(3); sq = f32(2) * n / N1 - f32(1)
+            v = j0((pa * np.sqrt((f32(1) - sq * sq).astype(np.float64)).astype(f32)).astype(np.float64)).astype(f32) / f32(j0(float(pa)))
+        elif name == "parzen":
+            q = n / N1
+            v = np.where(q <= f32(0.5), f32(1) - f32(6) * q * q * (f32(1) - q), f32(2) * (f32(1) - q) ** 3)
+        else:
+            raise ValueError(f"unknown FBP filter {name}")
+    v = np.asarray(v, np.float32); v[0] = 1.0
+    filt = (filt * v).astype(f32)
+    filt[w > PI] = 0
+    return filt
+
 
 class OracleMM:
     """CPU mirror of the reference's `multimodal` state machine

@@ -82,7 +82,7 @@ bp_kernel(const __grid_constant__ CUtensorMap tmS, const BpParams p)
                 const float ay0 = -fY0 * k.y, ay1 = -(fY0 + (float)(BP_TILE - 1)) * k.y;
                 const float fmin = fminf(ax0, ax1) + fminf(ay0, ay1) + k.z;
                 const int w0 = (int)floorf(fmin - 0.5f) - 1;
-                s_C[s * BP_TA + lane] = TTV_MAGIC - 128.0f - 256.0f * (float)w0;
+                s_C[s * BP_TA + lane] = TTV_MAGIC_C(w0);
                 tma_load_4d(smem_raw + (size_t)s * BP_STAGE_BYTES + (size_t)lane * BP_ANGLE_BYTES, &tmS, &full[s], 0, w0, a, xb);
             }
             __syncwarp();
@@ -118,15 +118,15 @@ bp_kernel(const __grid_constant__ CUtensorMap tmS, const BpParams p)
             const float Cl = s_C[s * BP_TA + l];
             const uint32_t base = smem_base + (uint32_t)s * BP_STAGE_BYTES + (uint32_t)l * BP_ANGLE_BYTES;
             const float myss = -__fmul_rn(fY, k.y);
-            const float ws = k.w * (1.0f / 256.0f);
-            const float w256 = 256.0f * ws;
+            const float ws = k.w * (1.0f / 512.0f);
+            const float w256 = 512.0f * ws;
 #pragma unroll
             for (int t = 0; t < BP_VT; ++t) {
                 const float fT = __fadd_rn(__fmaf_rn(fX[t], k.x, myss), k.z);
-                const float tt = __fmaf_rn(fT, 256.0f, Cl);
+                const float tt = __fmaf_rd(fT, 256.0f, Cl);
                 const uint32_t u = (uint32_t)(__float_as_int(tt) - TTV_MAGIC_BITS);
-                const uint32_t off = (u >> 8) << 7;
-                const float al = __int_as_float((int)((u & 255u) | 0x4B000000u)) - 8388608.0f;
+                const uint32_t off = (u >> 9) << 7;
+                const float al = __int_as_float((int)((u & 0x1FEu) | 0x4B000000u)) - 8388608.0f;
                 const float w1 = al * ws;
                 const float w0 = fmaf(-al, ws, w256);
                 const float4 v0 = lds128(base + off);

@@ -101,12 +101,16 @@ __device__ __forceinline__ void sts32(uint32_t addr, float v) {
 }
 
 // Texture-unit interpolation model (cudaFilterModeLinear, A/cuda/2d/util.cu:161-179,198-223):
-// the coordinate is converted to fixed point with 8 fractional bits (round to nearest), 0.5 is
-// subtracted, the integer part selects the texel pair and the 8-bit fraction is the weight.
-// t = fma(x, 256, C) with C = 1.5*2^23 - 128 - 256*w0 leaves  u = rint(256 x) - 128 - 256 w0  in the
-// low mantissa bits: u>>8 = texel index relative to the staged window start w0, u&255 = 256*alpha.
-#define TTV_MAGIC 12582912.0f       // 1.5 * 2^23
-#define TTV_MAGIC_BITS 0x4B400000
+// the coordinate is converted to fixed point with 8 fractional bits rounding HALF UP (floor(256 x + 0.5);
+// measured on B200 with scripts/probe/tex_probe.cu: 0 mismatches over 4.9 M coordinates including exact ties,
+// round-half-even fails on 7 %), 0.5 is subtracted, the integer part selects the texel pair and the
+// 8-bit fraction is the weight.
+// t = fma.rd(x, 256, C) with C = 1.5*2^22 + 0.5 - 128 - 256*w0 (floats in [2^22,2^23) have ulp 0.5, the
+// round-down FMA floors to it) leaves  u = floor(2*(256 x + 0.5 - 128 - 256 w0))  in the low mantissa bits:
+// u>>9 = texel index relative to the staged window start w0, u & 0x1FE = 2*256*alpha (weights in 1/512).
+#define TTV_MAGIC 6291456.0f        // 1.5 * 2^22
+#define TTV_MAGIC_BITS 0x4AC00000
+#define TTV_MAGIC_C(w0) ((TTV_MAGIC - 127.5f) - 256.0f * (float)(w0))
 
 __device__ __forceinline__ double warp_sum(double v) {
 #pragma unroll

@@ -384,17 +384,25 @@ public:
             q.rayX = rayX; q.rayY = rayY;
             q.vertical = std::fabs(rayX) <= std::fabs(rayY) ? 1 : 0;
             double ux = detUX, uy = detUY;
-            const double t = (ux * rayX + uy * rayY) / ((double)rayX * rayX + (double)rayY * rayY);
+            // float members multiplied / subtracted in float32 before the promotion to double, exactly as the
+            // reference's expressions evaluate (A/src/GeometryUtil2D.cpp:113, A/cuda/2d/par_bp.cu:174-178)
+            const volatile float rx2 = rayX * rayX, ry2 = rayY * rayY;
+            const volatile float rden = rx2 + ry2;
+            const double t = (ux * rayX + uy * rayY) / (double)rden;
             ux -= t * rayX; uy -= t * rayY;
             const double n2 = uy * uy + ux * ux;
             q.theta = (float)std::atan2(uy, ux);
             q.detsize = (float)std::sqrt(n2);
             q.offset = (float)(-0.5 * N - ((double)detSY * uy + (double)detSX * ux) / n2);
-            const double d = (double)detUX * rayY - (double)detUY * rayX;
+            const volatile float p1 = detUX * rayY, p2 = detUY * rayX;
+            const volatile float df = p1 - p2;
+            const double d = (double)df;
+            const volatile float q1 = detSY * rayX, q2 = detSX * rayY;
+            const volatile float nf = q1 - q2;
             q.sc = (float)(rayY / d);
             q.ss = (float)(-rayX / d);
-            q.off = (float)(((double)detSY * rayX - (double)detSX * rayY) / d);
-            q.scale = (float)(std::sqrt((double)rayX * rayX + (double)rayY * rayY) / std::fabs(d));
+            q.off = (float)((double)nf / d);
+            q.scale = (float)((double)std::sqrt((float)rden) / std::fabs(d));
         }
         // BP constants -> __constant__
         std::vector<float4> kb(Na);

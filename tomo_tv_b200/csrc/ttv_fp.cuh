@@ -82,7 +82,7 @@ fp_kernel(const __grid_constant__ CUtensorMap tmV, const __grid_constant__ CUten
             if (lane < TR) {
                 const int line = it * TR + lane;
                 const int w0 = w0tab[line];
-                s_C[s * TR + lane] = TTV_MAGIC - 128.0f - 256.0f * (float)w0;
+                s_C[s * TR + lane] = TTV_MAGIC_C(w0);
                 void* dst = smem_raw + (size_t)s * stage_bytes + (size_t)lane * line_bytes;
                 if (g.vertical) tma_load_4d(dst, tm, &full[s], 0, w0, line, xb);   // window along columns of row `line`
                 else            tma_load_4d(dst, tm, &full[s], 0, line, w0, xb);   // window along rows of column `line`
@@ -152,11 +152,11 @@ fp_kernel(const __grid_constant__ CUtensorMap tmV, const __grid_constant__ CUten
                 } else {
                     fP[t] = __fadd_rn(fP[t], step);
                 }
-                const float tt = __fmaf_rn(fP[t], 256.0f, Cl);
+                const float tt = __fmaf_rd(fP[t], 256.0f, Cl);
                 const uint32_t u = (uint32_t)(__float_as_int(tt) - TTV_MAGIC_BITS);
-                const uint32_t off = (u >> 8) << 7;
-                const float w1 = __int_as_float((int)((u & 255u) | 0x4B000000u)) - 8388608.0f;   // 256*alpha
-                const float w0 = 256.0f - w1;
+                const uint32_t off = (u >> 9) << 7;
+                const float w1 = __int_as_float((int)((u & 0x1FEu) | 0x4B000000u)) - 8388608.0f;   // 512*alpha
+                const float w0 = 512.0f - w1;
                 const float4 v0 = lds128(base + off);
                 const float4 v1 = lds128(base + off + 128u);
                 acc[t].x = fmaf(w1, v1.x, fmaf(w0, v0.x, acc[t].x));
@@ -173,7 +173,7 @@ fp_kernel(const __grid_constant__ CUtensorMap tmV, const __grid_constant__ CUten
     // ---------------- epilogue ----------------
     float part = 0.0f;
     if (angle_ok) {
-        const float cs = corr1 * (1.0f / 256.0f);
+        const float cs = corr1 * (1.0f / 512.0f);
 #pragma unroll
         for (int t = 0; t < FP_RT; ++t) {
             const int d = dbase + t;

@@ -43,7 +43,7 @@ __global__ void __launch_bounds__(256) sart_fp1_kernel(const Sart1Params p)
             f = __fadd_rn(f, -0.5f);
             fP = __fadd_rn(f, 0.5f);
         } else fP = __fadd_rn(fP, step);
-        const int q = __float2int_rn(fP * 256.0f) - 128;
+        const int q = __float2int_rd(fP * 256.0f + 0.5f) - 128;   // round half up (ttv_common.cuh)
         const int i = q >> 8;
         const float w1 = (float)(q & 255), w0 = 256.0f - w1;
         float4 v0 = make_float4(0.f, 0.f, 0.f, 0.f), v1 = v0;
@@ -75,7 +75,7 @@ __global__ void __launch_bounds__(256) sart_bp1_kernel(const SartBpParams p)
     const int Y = (int)(v / N), X = (int)(v % N);
     const float fX = (float)X - 0.5f * (float)N + 0.5f, fY = (float)Y - 0.5f * (float)N + 0.5f;
     const float fT = __fadd_rn(__fmaf_rn(fX, p.sc, -__fmul_rn(fY, p.ss)), p.off);
-    const int q = __float2int_rn(fT * 256.0f) - 128;
+    const int q = __float2int_rd(fT * 256.0f + 0.5f) - 128;   // round half up (ttv_common.cuh)
     const int i = q >> 8;
     const float w1 = (float)(q & 255) * (1.0f / 256.0f), w0 = 1.0f - w1;
     const int i0 = min(max(i, 0), p.Nd - 1), i1 = min(max(i + 1, 0), p.Nd - 1);     // Clamp addressing
