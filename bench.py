@@ -25,6 +25,9 @@ import numpy as np
 ROOT = os.path.dirname(os.path.abspath(__file__))
 sys.path.insert(0, ROOT)
 
+# dram__bytes_read.sum + dram__bytes_write.sum per launch, ncu --set full at 512^3 x 180 on 1 B200 (profiles/r1b_full_details.csv)
+TRAFFIC_512 = {"fgp_sweep": 3803738000, "fgp_first": 2109190000, "fgp_final": 2734996000, "momentum": 2624425000, "tv": 576208000,
+               "fp": 984207000, "bp": 1217342000}
 METRIC = "fista_tv_iters_per_sec"
 UNIT = "iterations/s"
 LAMBDA, NTV = 0.1, 10
@@ -102,6 +105,38 @@ def cpu_fista_sample(n, na, nslab, steps, warmup):
     for _ in range(steps):
         fista_iteration(o, st)
     return (time.perf_counter() - t0) / max(steps, 1), orc.lib().orc_num_threads()
+
+
+def ref_gpu_fista_sample(n, na, nslab, steps):
+    """The UNMODIFIED reference GPU engine (oracle/_ref/tomoengine*.so: tomo_TV's pybind11 class + its ASTRA fork,
+    built by oracle/build_ref.sh; test infrastructure) on a slab of `nslab` slices of the same problem.  The
+    reference loops over slices on the host (tomoengine.cpp:189-205), so its cost is linear in the slice count.
+    Returns seconds per iteration of the slab, or None when the extension is not available."""
+    ref_dir = os.path.join(ROOT, "oracle", "_ref")
+    if not os.path.isdir(ref_dir):
+        return None
+    sys.path.insert(0, ref_dir)
+    try:
+        import tomoengine as ref_mod
+    except Exception:
+        return None
+    import oracle as orc  # noqa: F401  (only to keep the leg inside the oracle/ boundary explicit)
+    from tomo_tv_b200.phantom import phantom3d, tilt_angles_deg
+    import tomo_tv_b200 as ttv
+    ang = np.deg2rad(tilt_angles_deg(na)).astype(np.float32)
+    x0 = (n - nslab) // 2
+    mk = ttv.tomoengine(nslab, n, ang)
+    mk.initialize_initial_volume(); mk.set_original_volume_all(phantom3d(n, n, x0=x0, count=nslab)); mk.create_projections()
+    b = mk.get_projections(); del mk
+    r = ref_mod.tomoengine(nslab, n, ang)
+    r.set_tilt_series(b)
+    r.initialize_fista(); r.initialize_FP(); r.restart_recon()
+    st = {"t": 1.0}
+    fista_iteration(r, st)
+    t0 = time.perf_counter()
+    for _ in range(steps):
+        fista_iteration(r, st)
+    return (time.perf_counter() - t0) / max(steps, 1)
 
 
 def run_reference(args):
@@ -244,12 +279,31 @@ def run_ours(args):
         if g in ("fp", "bp"):
             ent["samples_per_s"] = samples / (per * 1e-3)
         groups[g] = ent
-    dom = max(prof, key=lambda g: prof[g][0]) if prof else None
+    # `roofline`: the dominant HBM-bound kernel (fgp_tile_kernel, sweep mode: 8 launches per step).  The projector
+    # pair takes more of the step but is bound by shared-memory bandwidth, not HBM: it gets its own
+    # object against the LDS peak (SMs x 128 B/clk x measured SM clock); 8 B of shared memory per bilinear sample.
+    hbm_groups = [g for g in prof if g in alg_bytes and g not in ("fp", "bp")]
+    dom = max(hbm_groups, key=lambda g: prof[g][0]) if hbm_groups else None
     roof = None
-    if dom and dom in alg_bytes:
-        roof = {"kernel": dom, "bound": "hbm", "achieved": groups[dom]["achieved_gbs"], "peak": pk["hbm_gbs"], "unit": "GB/s",
-                "frac": groups[dom]["frac_of_hbm_peak"], "traffic": None, "peak_kind": pk_kind,
-                "algorithmic_bytes_per_launch": alg_bytes[dom]}
+    if dom:
+        roof = {"kernel": {"fgp_sweep": "fgp_tile_kernel<SWEEP>", "fgp_first": "fgp_tile_kernel<FIRST>", "fgp_final": "fgp_tile_kernel<FINAL>"}.get(dom, dom),
+                "bound": "hbm", "achieved": groups[dom]["achieved_gbs"], "peak": pk["hbm_gbs"], "unit": "GB/s",
+                "frac": groups[dom]["frac_of_hbm_peak"], "traffic": TRAFFIC_512.get(dom) if (n, na, world) == (512, 180, 1) else None, "peak_kind": pk_kind,
+                "algorithmic_bytes_per_launch": alg_bytes[dom], "share_of_step": groups[dom]["share_of_step"],
+                "traffic_note": "dram__bytes_read.sum + dram__bytes_write.sum per launch, ncu --set full at 512^3 x 180 on 1 GPU (profiles/r1b_dram_bytes.txt)"}
+    sm_mhz = (clk or {}).get("sm_mhz") or pk.get("sm_max_mhz") or 1965.0
+    try:
+        n_sm = torch.cuda.get_device_properties(local).multi_processor_count
+    except Exception:
+        n_sm = 148
+    lds_peak = n_sm * 128 * sm_mhz * 1e6 / 1e9
+    proj_roof = {}
+    for g in ("fp", "bp"):
+        if g in groups:
+            ach = samples * 8 / (groups[g]["ms_per_launch"] * 1e-3) / 1e9
+            proj_roof[g] = {"bound": "shared-memory", "achieved": ach, "peak": lds_peak, "unit": "GB/s", "frac": ach / lds_peak,
+                            "samples_per_s": groups[g]["samples_per_s"], "share_of_step": groups[g]["share_of_step"],
+                            "lds_bytes_per_sample": 8, "peak_def": f"{n_sm} SMs x 128 B/clk x {sm_mhz:.0f} MHz"}
     iter_bytes = world * (74 * V + 3 * S)
     iter_roof = {"algorithmic_bytes_per_iteration": iter_bytes, "achieved_gbs": iter_bytes / (ms_per_step * 1e-3) / 1e9,
                  "frac_of_hbm_peak_x_gpus": iter_bytes / (ms_per_step * 1e-3) / 1e9 / (pk["hbm_gbs"] * world)}
@@ -268,6 +322,7 @@ def run_ours(args):
             "gpu_launches": launches,
             "clocks": clk,
             "roofline": roof,
+            "projector_roofline": proj_roof,
             "kernels": groups,
             "iteration_roofline": iter_roof,
         }
@@ -277,6 +332,16 @@ def run_ours(args):
         sec, threads = cpu_fista_sample(n, na, nslab, 2, 1)
         line["cpu_baseline"] = {"value": (1.0 / sec) * (nslab / n), "unit": UNIT, "cores": threads, "kind": "port",
                                 "sample": f"{nslab} of {n} slices per step (2 timed iterations), scaled by {n}/{nslab}"}
+    if rank == 0 and world == 1 and not args.no_cpu:
+        nsl = min(32, n)
+        try:
+            sec = ref_gpu_fista_sample(n, na, nsl, 2)
+        except Exception as ex:  # the reference aborts the process on CUDA errors; anything catchable is reported
+            sec = None
+            line["reference_gpu"] = {"unavailable": str(ex)[:200]}
+        if sec is not None:
+            line["reference_gpu"] = {"value": (1.0 / sec) * (nsl / n), "unit": UNIT, "kind": "reference (oracle/_ref tomoengine + ASTRA fork, same B200)",
+                                     "sample": f"{nsl} central slices of {n} per step (2 timed iterations), scaled by {n}/{nsl}: the reference loops slices on the host"}
     if rank == 0:
         print(json.dumps(line), flush=True)
     del eng
