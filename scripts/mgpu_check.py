@@ -69,5 +69,34 @@ if rank == 0:
     print("MGPU_CHECK", "PASS" if ok else "FAIL", flush=True)
 dist.barrier()
 del eng
+
+# ---- the reference-facing layer under torchrun: TomoGPU on the sharded multigpuengine (config c3: SIRT + ASD-POCS)
+tmp = ttv.tomoengine(nx, n, ang, device=local)
+tmp.initialize_initial_volume(); tmp.set_original_volume_all(vol); tmp.create_projections()
+tilt = tmp.get_projections().reshape(nx, na, n).transpose(0, 2, 1)       # [Nslice, Nray, Nangles]
+del tmp
+deg = np.rad2deg(ang.astype(np.float64))
+
+
+def api_run(t):
+    out = {}
+    t.sirt(3, show_convergence=False); out["api_sirt"] = t.get_recon().copy(); out["api_sirt_cost"] = t.cost.copy()
+    t.asd_pocs(3, show_convergence=False); out["api_asd"] = t.get_recon().copy(); out["api_asd_tv"] = t.tv_vec.copy()
+    return out
+
+
+sh = ttv.TomoGPU(deg, tilt, verbose=False)
+assert isinstance(sh.tomo, ttv.multigpuengine) and sh.tomo.is_multi_gpu_enabled() and len(sh.tomo.get_gpu_ids()) == world
+got = api_run(sh)
+if rank == 0:
+    want = api_run(ttv.TomoGPU(deg, tilt, gpu_id=local, verbose=False))
+    for k, w in want.items():
+        err = float(np.linalg.norm((got[k] - w).ravel()) / max(np.linalg.norm(w.ravel()), 1e-30))
+        flag = err <= 2e-6
+        ok &= flag
+        print(f"mgpu[{world}] {k:12s} rel err {err:.3e} {'ok' if flag else 'FAIL'}", flush=True)
+    print("MGPU_API_CHECK", "PASS" if ok else "FAIL", flush=True)
+dist.barrier()
+del sh
 dist.destroy_process_group()
 sys.exit(0 if ok else 1)

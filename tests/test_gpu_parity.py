@@ -258,3 +258,30 @@ def test_errors_are_exceptions_not_aborts(ttv):
     e2 = ttv.tomoengine(4, 32)
     with pytest.raises(ttv.NativeError):
         e2.forward_projection()
+
+
+@pytest.mark.parametrize("n", [1024, 2048])
+def test_c5_inplane_size_operators_and_tv_vs_oracle(ttv, orc, n):
+    """BASELINE.json configs[4] in-plane size (2048 x 2048, the widest staged windows / most k-tiles) on a few
+    slices the CPU oracle finishes in seconds: FP, BP, one SIRT step, TV-FGP and the TV value."""
+    nx, na = 3, 12
+    rng = np.random.default_rng(n)
+    ang = np.deg2rad(np.linspace(-90, 90, na, endpoint=False) + 1.5).astype(np.float32)
+    eng = ttv.tomoengine(nx, n, ang)
+    o = _oracle_for(orc, eng, nx, n, ang)
+    vol = rng.random((nx, n, n), dtype=np.float32)
+    eng.set_recon_all(vol); o.recon[:] = vol
+    eng.forward_projection(); o.forward_projection()
+    assert S.rel_l2(eng.get_model_projections(), o.g) <= 1e-5
+    sino = rng.standard_normal((nx, na * n)).astype(np.float32)
+    eng.set_model_projections(sino); eng.back_projection()
+    assert S.rel_l2(eng.get_recon_all(), o.back_projection_of(sino)) <= 1e-5
+    for e in (eng, o):
+        e.set_tilt_series(o.g)
+        e.initialize_SIRT(); e.initialize_FP(); e.restart_recon()
+        e.SIRT(2)
+    assert S.rel_l2(eng.get_recon_all(), o.recon) <= 1e-5
+    tg, to = eng.tv_fgp(3, 0.1), o.tv_fgp(3, 0.1)
+    assert abs(tg - to) <= 1e-5 * abs(to)
+    assert S.rel_l2(eng.get_recon_all(), o.recon) <= 1e-5
+    assert abs(eng.tv() - o.tv()) <= 1e-5 * abs(o.tv())

@@ -5,6 +5,7 @@ Public surface (mirrors the reference, /root/reference/tomofusion):
     tomoengine                   tomofusion.gpu.utils.tomoengine (pybind11 class)
     ChemicalTomo                 tomofusion.chemistry.reconstructor.ChemicalTomo
     multimodal                   tomofusion.chemistry.utils.multimodal (pybind11 class)
+    multigpuengine               tomofusion.gpu.utils.multigpuengine (one rank per GPU under torchrun)
     pytvlib.initialize_algorithm / run / wbp_filters / sart_orders
     determine_gpu_config, device_count      tomofusion/__init__.py
 
@@ -16,6 +17,7 @@ from . import pytvlib  # noqa: F401
 from .reconstructor import TomoGPU  # noqa: F401
 from .fusion import multimodal  # noqa: F401
 from .chemistry import ChemicalTomo  # noqa: F401
+from .sharded import multigpuengine  # noqa: F401
 
 __version__ = "0.1.0"
 

@@ -261,14 +261,13 @@ class tomoengine:
     def setup_sharding(self, dist, rank, world, p2p=True):
         """NCCL communicator + (optionally) CUDA-IPC peer buffers, using an initialised
         torch.distributed process group for the rendezvous."""
-        uid = [tomoengine.nccl_unique_id() if rank == 0 else None]
-        dist.broadcast_object_list(uid, src=0)
-        self.comm_init(uid[0], rank, world)
+        from .sharded import exchange_handles
+        uid, left, right = exchange_handles(dist, rank, world, tomoengine.nccl_unique_id,
+                                            self.p2p_export() if (p2p and world > 1) else None)
+        self.comm_init(uid, rank, world)
         if p2p and world > 1:
-            handles = [None] * world
-            dist.all_gather_object(handles, self.p2p_export())
             # ring neighbours (the periodic TV value needs rank 0 <-> last); the FGP chain ignores the wrap-around
-            self.p2p_attach(handles[(rank - 1) % world], handles[(rank + 1) % world])
+            self.p2p_attach(left, right)
 
     # ---- measurement / test hooks (not part of the reference API) -------------------------------
     def sync(self):

@@ -56,16 +56,31 @@ class TomoGPU:
         self.Nslice, self.Nray, self.Nangles = np.shape(tiltSeries)
         if self.tiltAngles.size != self.Nangles:
             raise ValueError("number of tilt angles does not match tiltSeries.shape[2]")
-        # One engine drives one GPU.  With several GPUs the sharded engine (one process per
-        # GPU, tomo_tv_b200.sharded) is used by launching under torchrun; inside one process
-        # we run on `gpu_id` (or the current device).
+        # One engine drives one GPU.  The reference's 'multigpu' configuration (gpu_id < 0 and several
+        # GPUs, tomofusion/__init__.py:21-34) is one process per GPU here: under torchrun every rank
+        # builds the same TomoGPU on the full tilt series and owns a contiguous x-slab of it
+        # (tomo_tv_b200.sharded.multigpuengine); get_recon() returns the whole volume on every rank.
         ngpu = device_count()
         if ngpu == 0:
             raise ValueError('An Nvidia GPU is Needed for this package!')
-        self.tomo = tomoengine(self.Nslice, self.Nray, np.deg2rad(self.tiltAngles),
-                               device=gpu_id if gpu_id >= 0 else -1)
-        if gpu_id >= 0:
-            self.tomo.set_gpu(gpu_id)
+        self._dist = None
+        if gpu_id < 0:
+            try:
+                import torch.distributed as td
+                if td.is_available() and td.is_initialized() and td.get_world_size() > 1:
+                    self._dist = td
+            except ImportError:
+                pass
+        if self._dist is not None:
+            from .sharded import multigpuengine
+            self._say("Initializing multi-GPU configuration")
+            self.tomo = multigpuengine(self.Nslice, self.Nray, np.deg2rad(self.tiltAngles), dist=self._dist)
+        else:
+            self._say("Initializing single-GPU configuration")
+            self.tomo = tomoengine(self.Nslice, self.Nray, np.deg2rad(self.tiltAngles),
+                                   device=gpu_id if gpu_id >= 0 else -1)
+            if gpu_id >= 0:
+                self.tomo.set_gpu(gpu_id)
         self.set_tilt_series(tiltSeries)
         self.recon = None
         self.cost = None
@@ -76,7 +91,11 @@ class TomoGPU:
         if tuple(shp) != (self.Nslice, self.Nray, self.Nangles):
             raise ValueError("tilt series shape changed; build a new TomoGPU")
         self.recon = None
-        self.tomo.set_tilt_series(pack_tilt_series(tiltSeries))
+        b = pack_tilt_series(tiltSeries)
+        if self._dist is not None:
+            from .sharded import slab_of
+            b = slab_of(b, self._dist)
+        self.tomo.set_tilt_series(b)
 
     def _say(self, msg):
         if self.verbose:
@@ -184,5 +203,9 @@ class TomoGPU:
 
     def get_recon(self):
         """float64 [Nslice, Nray, Nray] like the reference (reconstructor.py:207-215), one bulk copy."""
-        self.recon = self.tomo.get_recon_all().astype(np.float64)
+        rec = self.tomo.get_recon_all()
+        if self._dist is not None:
+            from .sharded import gather_slabs
+            rec = gather_slabs(rec, self._dist)
+        self.recon = rec.astype(np.float64)
         return self.recon
