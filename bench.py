@@ -25,7 +25,7 @@ import numpy as np
 ROOT = os.path.dirname(os.path.abspath(__file__))
 sys.path.insert(0, ROOT)
 
-# dram__bytes_read.sum + dram__bytes_write.sum per launch, ncu --set full at 512^3 x 180 on 1 B200 (profiles/r1b_full_details.csv)
+# dram__bytes_read.sum + dram__bytes_write.sum per launch, ncu --set full at 512^3 x 180 on 1 B200 (profiles/r1h_dram_raw.csv)
 TRAFFIC_512 = {"fgp_sweep": 3803738000, "fgp_first": 2109190000, "fgp_final": 2734996000, "momentum": 2624425000, "tv": 576208000,
                "fp": 984207000, "bp": 1217342000}
 METRIC = "fista_tv_iters_per_sec"
@@ -207,7 +207,15 @@ def run_ours(args):
         eng.setup_sharding(dist, rank, world, p2p=os.environ.get("TTV_P2P", "1") != "0")
 
     # synthetic data: phantom slab -> tilt series by the engine's own forward projector
-    vol = phantom3d(n, n, x0=x0, count=nloc)
+    if args.phantom_period > 0:
+        # c5-sized runs (2048^3): evaluating every slice of the phantom on the host takes ~1 s per slice, so a
+        # block of `period` slices from the middle of this rank's slab is tiled along x instead
+        per = min(args.phantom_period, nloc)
+        blk = phantom3d(n, n, x0=x0 + (nloc - per) // 2, count=per)
+        vol = np.concatenate([blk] * ((nloc + per - 1) // per), axis=0)[:nloc]
+        del blk
+    else:
+        vol = phantom3d(n, n, x0=x0, count=nloc)
     eng.initialize_initial_volume()
     eng.set_original_volume_all(vol)
     eng.create_projections()
@@ -290,7 +298,7 @@ def run_ours(args):
                 "bound": "hbm", "achieved": groups[dom]["achieved_gbs"], "peak": pk["hbm_gbs"], "unit": "GB/s",
                 "frac": groups[dom]["frac_of_hbm_peak"], "traffic": TRAFFIC_512.get(dom) if (n, na, world) == (512, 180, 1) else None, "peak_kind": pk_kind,
                 "algorithmic_bytes_per_launch": alg_bytes[dom], "share_of_step": groups[dom]["share_of_step"],
-                "traffic_note": "dram__bytes_read.sum + dram__bytes_write.sum per launch, ncu --set full at 512^3 x 180 on 1 GPU (profiles/r1b_dram_bytes.txt)"}
+                "traffic_note": "dram__bytes_read.sum + dram__bytes_write.sum per launch, ncu --set full at 512^3 x 180 on 1 GPU (profiles/r1h_dram_raw.csv)"}
     sm_mhz = (clk or {}).get("sm_mhz") or pk.get("sm_max_mhz") or 1965.0
     try:
         n_sm = torch.cuda.get_device_properties(local).multi_processor_count
@@ -358,6 +366,7 @@ def main():
     ap.add_argument("--size", type=int, default=512)
     ap.add_argument("--angles", type=int, default=180)
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
+    ap.add_argument("--phantom-period", type=int, default=0, help="tile a block of this many phantom slices along x (large sizes)")
     args = ap.parse_args()
     if args.impl == "reference":
         run_reference(args)

@@ -199,6 +199,7 @@ int ttv_fista_momentum(ttv_handle h, float beta) {
         Engine::ProfScope ps(e, PF_MOMENTUM);
         momentum_kernel<<<ew_blocks(n4), 256, 0, e.st>>>(reinterpret_cast<float4*>(e.recon.p), reinterpret_cast<float4*>(e.yk.p),
                                                           reinterpret_cast<float4*>(e.recon_old.p), beta, n4);
+        std::swap(e.yk.p, e.recon_old.p);                    // y was written over recon_old; the old yk buffer holds x
     }
     ++e.launches; TTV_LAUNCH_CHECK();
     TTV_CATCH

@@ -264,6 +264,7 @@ __global__ void __launch_bounds__(256) tv_value_tiled_kernel(const float* __rest
                 vj[u] = (k < kend) ? rowj[(int64_t)k * 32] : 0.0f;
                 ve[u] = (ep && k < kend) ? ep[(int64_t)k * es] : 0.0f;
             }
+            float part = 0.0f;                       // 8 voxels in float, then one double add (F2F/DADD are quarter-rate)
 #pragma unroll
             for (int u = 0; u < 8; ++u) {
                 const int k = kb + u;
@@ -271,10 +272,11 @@ __global__ void __launch_bounds__(256) tv_value_tiled_kernel(const float* __rest
                 if (ep) vx = ve[u];
                 if (k < kend && valid) {
                     const float dx = c - vx, dy = c - vj[u], dz = c - vk[u];
-                    dtot += (double)sqrtf(1e-6f + dx * dx + dy * dy + dz * dz);
+                    part += sqrtf(1e-6f + dx * dx + dy * dy + dz * dz);
                 }
                 c = vk[u];
             }
+            dtot += (double)part;
         }
     }
     (void)tot;
