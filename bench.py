@@ -164,6 +164,10 @@ def run_reference(args):
 
 # ------------------------------------------------------------------------------------------------
 def run_ours(args):
+    # stdout carries exactly one JSON line: NCCL's "NCCL version ..." banner (NCCL_DEBUG=VERSION on the GPU
+    # boxes) is printed to stdout by rank 0, so keep only warnings unless the user asked for INFO/TRACE
+    if os.environ.get("NCCL_DEBUG", "").upper() in ("VERSION", ""):
+        os.environ["NCCL_DEBUG"] = "WARN"
     import torch
     import tomo_tv_b200 as ttv
     from tomo_tv_b200.phantom import phantom3d, tilt_angles_deg, slab_bounds
@@ -230,6 +234,7 @@ def run_ours(args):
     V, S, samples = eng.sizes()           # bytes of the local volume / sinogram slab
     eng.initialize_fista(); eng.initialize_FP(); eng.restart_recon()
     st = {"t": 1.0}
+    barrier()                                   # ranks finish their host-side set-up seconds apart at large sizes
     for _ in range(max(args.warmup, 3)):
         fista_iteration(eng, st)
 
@@ -366,8 +371,17 @@ def main():
     ap.add_argument("--size", type=int, default=512)
     ap.add_argument("--angles", type=int, default=180)
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
+    ap.add_argument("--max-seconds", type=float, default=1500.0, help="watchdog: hard-exit the process after this long")
     ap.add_argument("--phantom-period", type=int, default=0, help="tile a block of this many phantom slices along x (large sizes)")
     args = ap.parse_args()
+
+    def _watchdog():
+        # a rank stuck in a collective or a device wait after a peer died must not hold the box until the
+        # launcher's own limit: leave hard (no Python clean-up, which could block on the same device)
+        time.sleep(args.max_seconds)
+        sys.stderr.write(f"bench.py: watchdog fired after {args.max_seconds:.0f} s, exiting\n"); sys.stderr.flush()
+        os._exit(3)
+    threading.Thread(target=_watchdog, daemon=True).start()
     if args.impl == "reference":
         run_reference(args)
     else:

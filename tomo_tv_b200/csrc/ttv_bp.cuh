@@ -104,9 +104,9 @@ bp_kernel(const __grid_constant__ CUtensorMap tmS, const BpParams p)
 #pragma unroll
     for (int t = 0; t < BP_VT; ++t) fX[t] = (float)(Xb + t) - 0.5f * (float)N + 0.5f;
 
-    float4 acc[BP_VT];
+    Acc4 acc[BP_VT];
 #pragma unroll
-    for (int t = 0; t < BP_VT; ++t) acc[t] = make_float4(0.f, 0.f, 0.f, 0.f);
+    for (int t = 0; t < BP_VT; ++t) acc[t].zero();
     const uint32_t smem_base = smem_u32(smem_raw) + (uint32_t)lx * 16u;
 
     for (int it = 0; it < nst; ++it) {
@@ -131,10 +131,8 @@ bp_kernel(const __grid_constant__ CUtensorMap tmS, const BpParams p)
                 const float w0 = fmaf(-al, ws, w256);
                 const float4 v0 = lds128(base + off);
                 const float4 v1 = lds128(base + off + 128u);
-                acc[t].x = fmaf(w1, v1.x, fmaf(w0, v0.x, acc[t].x));
-                acc[t].y = fmaf(w1, v1.y, fmaf(w0, v0.y, acc[t].y));
-                acc[t].z = fmaf(w1, v1.z, fmaf(w0, v0.z, acc[t].z));
-                acc[t].w = fmaf(w1, v1.w, fmaf(w0, v0.w, acc[t].w));
+                acc[t].fma(w0, v0);          // acc = fmaf(w1, v1, fmaf(w0, v0, acc)), 4 FFMA2
+                acc[t].fma(w1, v1);
             }
         }
         __syncwarp();
@@ -148,7 +146,7 @@ bp_kernel(const __grid_constant__ CUtensorMap tmS, const BpParams p)
             const int X = Xb + t;
             if (X < N) {
                 const size_t o = (((size_t)xb * N + Y) * N + X) * TTV_XI + lx * 4;
-                float4 r = acc[t];
+                float4 r = acc[t].get();
                 if (EPI != BP_STORE) {
                     const float4 x = *reinterpret_cast<const float4*>(p.vol + o);
                     if (EPI == BP_SIRT_UPD) {

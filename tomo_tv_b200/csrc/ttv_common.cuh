@@ -85,6 +85,31 @@ __device__ __forceinline__ void tma_load_4d(void* dst, const CUtensorMap* tm, ui
 __device__ __forceinline__ void tma_prefetch_desc(const CUtensorMap* tm) {
     asm volatile("prefetch.tensormap [%0];" ::"l"(tm) : "memory");
 }
+// Four fp32 accumulators held as two packed pairs for sm_100a's FFMA2 (fma.rn.f32x2: two IEEE-754 fused
+// multiply-adds per instruction, bit-identical to two fmaf; the scalar weight is broadcast by the instruction
+// itself, `FFMA2 R, Rw.F32, Rv.F32x2, Racc.F32x2`).  The projectors issue 4 FFMA2 instead of 8 FFMA per
+// bilinear sample group, which frees issue slots next to the LDS.128 stream that bounds them.
+struct Acc4 {
+    unsigned long long lo, hi;          // {x, y}, {z, w}
+    __device__ __forceinline__ void zero() { lo = 0ull; hi = 0ull; }
+    // this += w * v   (per component: fmaf(w, v, acc))
+    __device__ __forceinline__ void fma(float w, const float4& v) {
+        asm("{\n\t.reg .b64 ww, vv;\n\t"
+            "mov.b64 ww, {%2, %2};\n\t"
+            "mov.b64 vv, {%3, %4};\n\t"
+            "fma.rn.f32x2 %0, ww, vv, %0;\n\t"
+            "mov.b64 vv, {%5, %6};\n\t"
+            "fma.rn.f32x2 %1, ww, vv, %1;\n\t}"
+            : "+l"(lo), "+l"(hi) : "f"(w), "f"(v.x), "f"(v.y), "f"(v.z), "f"(v.w));
+    }
+    __device__ __forceinline__ float4 get() const {
+        float4 r;
+        asm("mov.b64 {%0, %1}, %2;" : "=f"(r.x), "=f"(r.y) : "l"(lo));
+        asm("mov.b64 {%0, %1}, %2;" : "=f"(r.z), "=f"(r.w) : "l"(hi));
+        return r;
+    }
+};
+
 __device__ __forceinline__ float4 lds128(uint32_t addr) {
     float4 v;
     asm volatile("ld.shared.v4.f32 {%0,%1,%2,%3}, [%4];" : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w) : "r"(addr));

@@ -92,7 +92,8 @@ __global__ void wait_flags_kernel(const unsigned* fl, const unsigned* fr, unsign
             unsigned v;
             asm volatile("ld.acquire.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(f) : "memory");
             if ((int)(v - epoch) >= 0) break;
-            if (clock64() - t0 > 4000000000LL) { err[0] = 1; err[1] = side; err[2] = (int)v; err[3] = (int)epoch; return; }
+            // ~2 minutes of SM clocks: ranks may reach their first sweep seconds apart (host-side set-up skew)
+            if (clock64() - t0 > 240000000000LL) { err[0] = 1; err[1] = side; err[2] = (int)v; err[3] = (int)epoch; return; }
             __nanosleep(200);
         }
     }
@@ -818,8 +819,14 @@ public:
         const size_t n = vol_elems();
         // every allocation first: cudaMalloc may synchronise the device, which must not happen while a
         // wait kernel of this call spins on a neighbour's epoch
+        bool fresh = !scratch.ok();
         if (!scratch.ok()) scratch.alloc(n);
-        for (int i = 0; i < 6; ++i) if (!P[i].ok() && iter > 1) P[i].alloc(n);
+        for (int i = 0; i < 6; ++i) if (!P[i].ok() && iter > 1) { P[i].alloc(n); fresh = true; }
+        // ... and not on a NEIGHBOUR either: with peer access enabled a cudaMalloc maps the new memory on the peer
+        // devices, which can wait for a peer GPU that is itself spinning on this rank's epoch (seen at 2048^3 on
+        // 8 GPUs, 7 x 4 GiB allocated in the first call).  Every rank allocates in the same call, so one
+        // all-reduce here means "all ranks have finished allocating" before any rank starts to spin.
+        if (fresh && nranks > 1 && comm) (void)allreduce_sum(0.0);
         // slice 0 of the right neighbour (ring): serves the periodic TV value, the TV map and -- on all but the
         // last rank -- the non-periodic FGP chain (`in` is constant over the sweeps): one exchange per call
         const float* hn = nullptr;

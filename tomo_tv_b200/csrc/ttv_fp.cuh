@@ -124,9 +124,9 @@ fp_kernel(const __grid_constant__ CUtensorMap tmV, const __grid_constant__ CUten
         m[t] = __fmul_rn(t1, detStep);
         fP[t] = 0.0f;
     }
-    float4 acc[FP_RT];
+    Acc4 acc[FP_RT];
 #pragma unroll
-    for (int t = 0; t < FP_RT; ++t) acc[t] = make_float4(0.f, 0.f, 0.f, 0.f);
+    for (int t = 0; t < FP_RT; ++t) acc[t].zero();
 
     const uint32_t smem_base = smem_u32(smem_raw) + (uint32_t)lx * 16u;
     const float halfN = 0.5f * (float)N;
@@ -159,10 +159,8 @@ fp_kernel(const __grid_constant__ CUtensorMap tmV, const __grid_constant__ CUten
                 const float w0 = 512.0f - w1;
                 const float4 v0 = lds128(base + off);
                 const float4 v1 = lds128(base + off + 128u);
-                acc[t].x = fmaf(w1, v1.x, fmaf(w0, v0.x, acc[t].x));
-                acc[t].y = fmaf(w1, v1.y, fmaf(w0, v0.y, acc[t].y));
-                acc[t].z = fmaf(w1, v1.z, fmaf(w0, v0.z, acc[t].z));
-                acc[t].w = fmaf(w1, v1.w, fmaf(w0, v0.w, acc[t].w));
+                acc[t].fma(w0, v0);          // acc = fmaf(w1, v1, fmaf(w0, v0, acc)), 4 FFMA2
+                acc[t].fma(w1, v1);
             }
         }
         __syncwarp();
@@ -180,7 +178,8 @@ fp_kernel(const __grid_constant__ CUtensorMap tmV, const __grid_constant__ CUten
             if (d < p.Nd) {
                 const size_t cell = ((size_t)xb * p.Na + A.orig) * p.Nd + d;
                 const size_t o = cell * TTV_XI + lx * 4;
-                float4 ax = make_float4(acc[t].x * cs, acc[t].y * cs, acc[t].z * cs, acc[t].w * cs);
+                const float4 a4 = acc[t].get();
+                float4 ax = make_float4(a4.x * cs, a4.y * cs, a4.z * cs, a4.w * cs);
                 float4 r;
                 if (EPI == FP_STORE) {
                     r = ax;
