@@ -285,3 +285,44 @@ def test_c5_inplane_size_operators_and_tv_vs_oracle(ttv, orc, n):
     assert abs(tg - to) <= 1e-5 * abs(to)
     assert S.rel_l2(eng.get_recon_all(), o.recon) <= 1e-5
     assert abs(eng.tv() - o.tv()) <= 1e-5 * abs(o.tv())
+
+
+def test_momentum_sequence_matches_numpy(ttv):
+    """Three consecutive fista_momentum calls (the kernel writes y over recon_old and the engine swaps the
+    yk / recon_old buffers): recon, yk and recon_old must follow tomoengine.cpp:381-384 step after step.
+    yk is driven through soft_threshold, which acts on yk under momentum (tomoengine.cpp:436-438)."""
+    nx, n = 35, 40
+    rng = np.random.default_rng(11)
+    a = rng.random((nx, n, n), dtype=np.float32)
+    eng = ttv.tomoengine(nx, n, np.array([0.0, 0.4], np.float32))
+    eng.initialize_initial_volume(); eng.set_recon_all(a)
+    eng.initialize_fista()                                     # yk = recon_old = a
+    yk, old = a.astype(np.float64), a.astype(np.float64)
+    lam = np.float32(0.05)
+    for beta in (0.0, 0.28, 0.43):
+        eng.soft_threshold(float(lam))                         # yk <- max(shrink(yk, lam), 0)
+        yk = np.maximum(np.sign(yk) * np.maximum(np.abs(yk) - np.float64(lam), 0.0), 0.0).astype(np.float32).astype(np.float64)
+        eng.fista_momentum(beta)
+        recon = yk.copy()
+        y = (np.float64(np.float32(beta)) * (yk - old).astype(np.float32).astype(np.float64) + yk).astype(np.float32).astype(np.float64)
+        old, yk = recon, y
+        got = eng.get_recon_all()
+        assert np.max(np.abs(got - recon)) <= 2.5e-7
+    # yk itself: one more threshold + momentum(0) copies it into recon
+    eng.soft_threshold(0.0); eng.fista_momentum(0.0)
+    assert np.max(np.abs(eng.get_recon_all() - np.maximum(yk, 0.0))) <= 2.5e-7
+
+
+def test_multigpuengine_without_process_group_is_a_single_gpu_engine(ttv):
+    nx, n, na = 9, 32, 6
+    ang = np.deg2rad(np.linspace(-60, 60, na)).astype(np.float32)
+    rng = np.random.default_rng(4)
+    b = rng.random((nx, na * n), dtype=np.float32)
+    outs = []
+    for cls in (ttv.tomoengine, ttv.multigpuengine):
+        e = cls(nx, n, ang)
+        e.set_tilt_series(b); e.initialize_SIRT(); e.SIRT(2)
+        outs.append(e.get_recon_all())
+    assert np.array_equal(outs[0], outs[1])
+    m = ttv.multigpuengine(nx, n, ang)
+    assert m.is_multi_gpu_enabled() is False and len(m.get_gpu_ids()) == 1 and m.global_nslice == nx
