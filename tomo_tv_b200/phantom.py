@@ -63,3 +63,31 @@ def slab_bounds(nslice, nranks, rank):
     first = rank * base + min(rank, rem)
     count = base + (1 if rank < rem else 0)
     return first, count
+
+
+# modified Shepp-Logan head phantom (Toft 1996): amplitude, semi-axes a, b, centre x0, y0, rotation [deg]
+_SHEPP_LOGAN_2D = [
+    (1.00, 0.6900, 0.9200, 0.00, 0.0000, 0.0),
+    (-0.80, 0.6624, 0.8740, 0.00, -0.0184, 0.0),
+    (-0.20, 0.1100, 0.3100, 0.22, 0.0000, -18.0),
+    (-0.20, 0.1600, 0.4100, -0.22, 0.0000, 18.0),
+    (0.10, 0.2100, 0.2500, 0.00, 0.3500, 0.0),
+    (0.10, 0.0460, 0.0460, 0.00, 0.1000, 0.0),
+    (0.10, 0.0460, 0.0460, 0.00, -0.1000, 0.0),
+    (0.10, 0.0460, 0.0230, -0.08, -0.6050, 0.0),
+    (0.10, 0.0230, 0.0230, 0.00, -0.6060, 0.0),
+    (0.10, 0.0230, 0.0460, 0.06, -0.6050, 0.0),
+]
+
+
+def shepp_logan_2d(n):
+    """n x n modified Shepp-Logan phantom, float32, values in [0, 1] (BASELINE.json configs[0])."""
+    c = (np.arange(n, dtype=np.float64) + 0.5) / n * 2 - 1
+    X, Y = np.meshgrid(c, -c)                 # x to the right, y up
+    img = np.zeros((n, n))
+    for amp, a, b, x0, y0, rot in _SHEPP_LOGAN_2D:
+        t = np.deg2rad(rot)
+        xr = (X - x0) * np.cos(t) + (Y - y0) * np.sin(t)
+        yr = -(X - x0) * np.sin(t) + (Y - y0) * np.cos(t)
+        img += amp * ((xr / a) ** 2 + (yr / b) ** 2 <= 1.0)
+    return np.clip(img, 0.0, 1.0).astype(np.float32)
