@@ -69,3 +69,20 @@ def test_phantom_is_deterministic(ttv):
     assert a.dtype == np.float32 and a.shape == (6, 32, 32) and np.array_equal(a, b)
     assert a.min() >= 0 and 0.2 < float(a.max()) <= 1.0
     assert np.array_equal(phantom3d(6, 32, x0=2, count=3), a[2:5])
+
+
+def test_tomogpu_get_projections_inverts_the_packing(ttv):
+    """TomoGPU.get_projections (a `pass` stub in the reference, reconstructor.py:217-219) returns the tilt
+    series in the constructor's [Nslice, Nray, Nangles] layout."""
+    from tomo_tv_b200.reconstructor import pack_tilt_series, TomoGPU
+    ts = np.random.default_rng(0).random((4, 6, 3)).astype(np.float32)
+
+    class FakeEngine:
+        def get_projections(self):
+            return pack_tilt_series(ts)
+
+    t = TomoGPU.__new__(TomoGPU)
+    t.tomo, t.Nangles, t.Nray = FakeEngine(), 3, 6
+    assert np.array_equal(t.get_projections(), ts)
+    with pytest.raises(RuntimeError):
+        t.show_recon()

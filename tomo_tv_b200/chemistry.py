@@ -180,3 +180,8 @@ class ChemicalTomo:
             ax.plot(s); ax.set_ylabel(l); ax.set_xlim([0, max(len(s) - 1, 1)])
         plt.xlabel('# Iterations')
         plt.show()
+
+    def display_recon(self):
+        """The reference's Tkinter element viewer (chemistry/reconstructor.py:251-...) is UI, outside the scope
+        of this package: fetch the 4-D array with get_recon()."""
+        raise RuntimeError("display_recon: the Tk viewer is not part of tomo_tv_b200; use get_recon()")

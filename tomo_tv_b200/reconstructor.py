@@ -209,3 +209,15 @@ class TomoGPU:
             rec = gather_slabs(rec, self._dist)
         self.recon = rec.astype(np.float64)
         return self.recon
+
+    def get_projections(self):
+        """The measured tilt series as the constructor takes it, float32 [Nslice, Nray, Nangles]
+        (a `pass` stub in the reference, reconstructor.py:217-219; with several ranks: this rank's slab)."""
+        b = self.tomo.get_projections()
+        return np.ascontiguousarray(b.reshape(b.shape[0], self.Nangles, self.Nray).transpose(0, 2, 1))
+
+    def show_recon(self):
+        """The reference's Tkinter slice viewer (reconstructor.py:221-383) is UI, outside the scope of this
+        package: fetch the volume with get_recon() and view it with the tool of your choice."""
+        raise RuntimeError("show_recon: the Tk viewer is not part of tomo_tv_b200; use get_recon()")
+
