@@ -371,7 +371,7 @@ def main():
     ap.add_argument("--size", type=int, default=512)
     ap.add_argument("--angles", type=int, default=180)
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
-    ap.add_argument("--max-seconds", type=float, default=1500.0, help="watchdog: hard-exit the process after this long")
+    ap.add_argument("--max-seconds", type=float, default=900.0, help="watchdog: hard-exit the process after this long")
     ap.add_argument("--phantom-period", type=int, default=0, help="tile a block of this many phantom slices along x (large sizes)")
     args = ap.parse_args()
 
@@ -382,10 +382,21 @@ def main():
         sys.stderr.write(f"bench.py: watchdog fired after {args.max_seconds:.0f} s, exiting\n"); sys.stderr.flush()
         os._exit(3)
     threading.Thread(target=_watchdog, daemon=True).start()
-    if args.impl == "reference":
-        run_reference(args)
-    else:
-        run_ours(args)
+    try:
+        if args.impl == "reference":
+            run_reference(args)
+        else:
+            run_ours(args)
+    except BaseException:
+        # under torchrun a rank that fails must go away at once: interpreter shutdown can block on a device
+        # that still runs a peer wait / NCCL kernel, and the launcher only tears the other ranks down (they are
+        # waiting for this one) when it sees this process exit
+        import traceback
+        traceback.print_exc()
+        sys.stderr.flush(); sys.stdout.flush()
+        if int(os.environ.get("WORLD_SIZE", "1")) > 1:
+            os._exit(1)
+        raise
 
 
 if __name__ == "__main__":

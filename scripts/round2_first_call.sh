@@ -1,0 +1,14 @@
+# First GPU call of the next round (ONE GPU): validates everything changed after the last round-1 measurement
+# (FFMA2 projector accumulators, 4V momentum, TV float partials, first-call all-reduce) and refreshes the
+# evidence.  Every step has its own short timeout; nothing here can hold the box for long.
+mkdir -p gpurun_out
+timeout -k 10 900 python -m pytest tests -m gpu -x -q --timeout 600 > gpurun_out/r2a_pytest_gpu.log 2>&1; echo "pytest exit $?"
+tail -n 5 gpurun_out/r2a_pytest_gpu.log | cut -c1-300
+timeout -k 10 300 python -c "import __graft_entry__ as g; g.smoke()" > gpurun_out/r2a_smoke.log 2>&1; echo "smoke exit $?"; tail -n 2 gpurun_out/r2a_smoke.log
+timeout -k 10 600 python bench.py --steps 20 --warmup 3 > gpurun_out/r2a_bench512.json 2> gpurun_out/r2a_bench512.err; echo "bench exit $?"
+cut -c1-400 gpurun_out/r2a_bench512.json
+timeout -k 10 600 ncu --metrics gpu__time_duration.sum --clock-control none -c 400 --csv --log-file gpurun_out/r2a_launches_bench512.csv python bench.py --steps 2 --warmup 3 --no-cpu > gpurun_out/r2a_ncu_launch.log 2>&1; echo "ncu launches exit $?"
+timeout -k 10 900 ncu --set full --clock-control none --import-source on -k regex:'fgp_tile|fp_kernel|bp_kernel|tv_value|momentum' -s 30 -c 16 -o gpurun_out/r2a_full python bench.py --steps 2 --warmup 3 --no-cpu > gpurun_out/r2a_ncu_full.log 2>&1; echo "ncu full exit $?"
+ncu -i gpurun_out/r2a_full.ncu-rep --page details --csv > gpurun_out/r2a_full_details.csv 2>/dev/null
+ncu -i gpurun_out/r2a_full.ncu-rep --page raw --csv --metrics dram__bytes_read.sum,dram__bytes_write.sum,gpu__time_duration.sum > gpurun_out/r2a_dram_raw.csv 2>/dev/null
+rm -f gpurun_out/r2a_full.ncu-rep
