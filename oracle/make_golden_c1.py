@@ -6,7 +6,7 @@ Test infrastructure.  Runs IN THE BUILD CONTAINER only (needs /root/reference): 
 skimage / h5py, which this image lacks, so the two functions are pulled out of the parsed source) builds the
 measurement matrix, and the reference's compiled engine oracle/_ref/ctvlib*.so (oracle/build_ref.sh) creates
 the projections and reconstructs, following tomofusion/cpu/sim_tomo.py:14-19,38-60 (beta0 = 0.5, x0.995 per
-iteration, 100 iterations of ART; SIRT with beta = 1/lipschits).  Writes tests/golden/c1_cpu_reference.npz.
+iteration, 100 iterations of ART; SIRT with beta = 1/lipschits).  Writes tests/golden/cpuref_c1.npz.
 """
 import ast
 import os
@@ -64,7 +64,7 @@ def main():
         if alg == "ART":
             out["b"] = np.asarray(tomo.get_projections(), np.float32)       # [1, Na*N]
         print(f"{alg}: {niter} iterations in {sec:.2f} s ({niter / sec:.1f} it/s, 1 slice -> 1 core), rmse {rm[-1]:.4f}, dd {dd[-1]:.4f}")
-    np.savez_compressed(os.path.join(ROOT, "tests", "golden", "c1_cpu_reference.npz"), **out)
+    np.savez_compressed(os.path.join(ROOT, "tests", "golden", "cpuref_c1.npz"), **out)
 
 
 if __name__ == "__main__":

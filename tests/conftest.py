@@ -53,7 +53,7 @@ def golden_cases():
         return []
     out = []
     for f in sorted(os.listdir(GOLDEN)):
-        if f.endswith(".npz") and not f.endswith("_inputs.npz") and not f.startswith("fusion_"):
+        if f.endswith(".npz") and not f.endswith("_inputs.npz") and not f.startswith(("fusion_", "cpuref_")):
             geom, scn = f[:-4].split("_", 1)
             out.append((geom, scn))
     return out

@@ -1,6 +1,6 @@
 """BASELINE.json configs[0]: 2-D Shepp-Logan 256^2 x 60 angles, reconstructed by the reference's own CPU
 package (tomofusion/cpu: Siddon system matrix from parallelRay + ART / SIRT in ctvlib.cpp).  The golden file
-tests/golden/c1_cpu_reference.npz was produced by oracle/make_golden_c1.py from the unmodified reference.
+tests/golden/cpuref_c1.npz was produced by oracle/make_golden_c1.py from the unmodified reference.
 
 The CPU package discretises the projector differently (exact ray / pixel intersection lengths) from the GPU
 path this repo replaces (ASTRA's Joseph kernels with 8-bit texture weights), and ART (row action) is not SART
@@ -19,7 +19,7 @@ N, NA = 256, 60
 
 
 def _load():
-    g = np.load(os.path.join(GOLDEN, "c1_cpu_reference.npz"))
+    g = np.load(os.path.join(GOLDEN, "cpuref_c1.npz"))
     from tomo_tv_b200.phantom import shepp_logan_2d
     return g, shepp_logan_2d(N), np.deg2rad(g["angles_deg"]).astype(np.float32)
 
