@@ -12,3 +12,6 @@ timeout -k 10 900 ncu --set full --clock-control none --import-source on -k rege
 ncu -i gpurun_out/r2a_full.ncu-rep --page details --csv > gpurun_out/r2a_full_details.csv 2>/dev/null
 ncu -i gpurun_out/r2a_full.ncu-rep --page raw --csv --metrics dram__bytes_read.sum,dram__bytes_write.sum,gpu__time_duration.sum > gpurun_out/r2a_dram_raw.csv 2>/dev/null
 rm -f gpurun_out/r2a_full.ncu-rep
+# secondary workloads (SIRT, SART pass, KL, CGLS, ASD-POCS iteration, FBP): first measurements of the non-headline paths
+timeout -k 10 600 python scripts/bench_algos.py --steps 3 > gpurun_out/r2a_bench_algos.jsonl 2> gpurun_out/r2a_bench_algos.err; echo "bench_algos exit $?"
+cut -c1-200 gpurun_out/r2a_bench_algos.jsonl
