@@ -325,6 +325,10 @@ int ttv_set_option(ttv_handle h, const char* name, int value) {
     Engine& e = E(h);
     const std::string nm = name ? name : "";
     if (nm == "fgp_tiled") e.fgp_tiled = value != 0;
+    else if (nm == "bp_variant") {
+        if (value != 4 && value != 8) throw CudaError("ttv_set_option: bp_variant must be 4 (default) or 8 (experimental)");
+        e.bp_variant = value;
+    }
     else throw CudaError("ttv_set_option: unknown option '" + nm + "'");
     TTV_CATCH
 }

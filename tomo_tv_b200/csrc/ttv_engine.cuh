@@ -9,6 +9,7 @@
 #include "ttv_common.cuh"
 #include "ttv_fp.cuh"
 #include "ttv_bp.cuh"
+#include "ttv_bp8.cuh"
 #include "ttv_tv.cuh"
 #include "ttv_fgp.cuh"
 #include "ttv_elem.cuh"
@@ -525,6 +526,11 @@ public:
         TTV_CUDA(cudaFuncSetAttribute(bp_kernel<BP_STEP_UPD>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)BP_SMEM));
         TTV_CUDA(cudaFuncSetAttribute(bp_kernel<BP_ADD>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)BP_SMEM));
         TTV_CUDA(cudaFuncSetAttribute(bp_kernel<BP_FUSE_UPD>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)BP_SMEM));
+        TTV_CUDA(cudaFuncSetAttribute(bp8_kernel<BP_STORE>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)BP8_SMEM));
+        TTV_CUDA(cudaFuncSetAttribute(bp8_kernel<BP_SIRT_UPD>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)BP8_SMEM));
+        TTV_CUDA(cudaFuncSetAttribute(bp8_kernel<BP_STEP_UPD>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)BP8_SMEM));
+        TTV_CUDA(cudaFuncSetAttribute(bp8_kernel<BP_ADD>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)BP8_SMEM));
+        TTV_CUDA(cudaFuncSetAttribute(bp8_kernel<BP_FUSE_UPD>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)BP8_SMEM));
     }
 
     // c_bp_angle is one __constant__ table per device: engines with different angle sets (HAADF / chemical
@@ -568,12 +574,22 @@ public:
         bind_bp_constants();
         BpParams p; if (extra) p = *extra;
         p.N = N; p.Nd = N; p.Na = Na; p.vol = vol; p.C = C.p; p.step = step;
+        if (bp_variant == 8) {
+            // experimental variant (ttv_bp8.cuh): 32 x 24 tile, 8 slices per lane, register reuse along the voxel run
+            CUtensorMap tm8 = make_tmap(sino, N, Na, zb, BP8_CW, 1);
+            dim3 grid8((N + BP8_TX - 1) / BP8_TX, (N + BP8_TY - 1) / BP8_TY, zb);
+            ProfScope ps(*this, PF_BP);
+            bp8_kernel<EPI><<<grid8, BP8_THREADS, BP8_SMEM, st>>>(tm8, p);
+            TTV_LAUNCH_CHECK(); ++launches;
+            return;
+        }
         const int nt = (N + BP_TILE - 1) / BP_TILE;
         dim3 grid(nt, nt, zb);
         ProfScope ps(*this, PF_BP);
         bp_kernel<EPI><<<grid, BP_THREADS, BP_SMEM, st>>>(tmS, p);
         TTV_LAUNCH_CHECK(); ++launches;
     }
+    int bp_variant = 4;             // 4: bp_kernel (default, validated); 8: bp8_kernel (experimental, ttv_set_option)
 
     double read_red(int slot) {
         double v; TTV_CUDA(cudaMemcpyAsync(&v, d_red + slot, sizeof(double), cudaMemcpyDeviceToHost, st)); sync();
