@@ -13,15 +13,15 @@ pytestmark = [pytest.mark.gpu,
 
 @pytest.mark.parametrize("nx,n,na", [(5, 40, 7), (33, 72, 17), (64, 128, 40), (40, 200, 24), (3, 512, 12)])
 def test_bp_variant_8_matches_default(ttv, nx, n, na):
-    """bp8_kernel (ttv_bp8.cuh: 8 slices per lane, register reuse along the voxel run) performs the same
-    operations in the same order per sample as bp_kernel: back projection, the fused SIRT update and the KL step
-    must be bit-identical."""
+    """bp8_kernel (ttv_bp8.cuh: 8 slices per lane, register reuse along the voxel run).  FORM 0 (variant 8) performs
+    the same operations in the same order per sample as bp_kernel: back projection, the fused SIRT update and the
+    KL step must be bit-identical.  FORM 1 (variant 9) may differ by one rounding per sample."""
     rng = np.random.default_rng(nx * 7 + n)
     ang = np.sort(rng.uniform(-np.pi / 2, np.pi / 2, na)).astype(np.float32)
     sino = rng.standard_normal((nx, na * n)).astype(np.float32)
     b = rng.random((nx, na * n), dtype=np.float32) * 3
     outs = []
-    for variant in (4, 8):
+    for variant in (4, 8, 9):
         eng = ttv.tomoengine(nx, n, ang)
         eng.set_option("bp_variant", variant)
         eng.initialize_initial_volume()
@@ -36,3 +36,7 @@ def test_bp_variant_8_matches_default(ttv, nx, n, na):
     for a, c in zip(outs[0][:3], outs[1][:3]):
         assert np.array_equal(a, c)
     assert outs[0][3] == outs[1][3]
+    # variant 9 (parity registers) adds the two taps of a sample even-cell-first: one rounding of the partial sum
+    for a, c in zip(outs[0][:3], outs[2][:3]):
+        assert np.linalg.norm((a - c).ravel()) <= 1e-6 * np.linalg.norm(a.ravel())
+    assert np.allclose(outs[0][3], outs[2][3], rtol=1e-5)

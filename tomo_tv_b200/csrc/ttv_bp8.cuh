@@ -63,7 +63,13 @@ __device__ __forceinline__ float4 bp_apply(const BpParams& p, size_t o, float4 r
     }
 }
 
-template <int EPI>
+// FORM 0: the cell pair (c, c+1) lives in registers a*, b* and is shifted by register moves when the voxel run
+//         crosses a cell; operations and their order are those of bp_kernel (bit-identical results).
+// FORM 1: "parity registers" -- the even cell lives in e*, the odd cell in o*, a cell that is already held is not
+//         reloaded and nothing is ever moved; the weights are swapped by the parity of c instead.  The two FMAs of
+//         a sample are then issued even-cell-first, i.e. in the other order whenever c is odd: same values to
+//         within one rounding of the partial sum (checked against FORM 0 with a tolerance, not bit-exactly).
+template <int EPI, int FORM>
 __global__ void __launch_bounds__(BP8_THREADS, 1)
 bp8_kernel(const __grid_constant__ CUtensorMap tmS, const BpParams p)
 {
@@ -139,8 +145,9 @@ bp8_kernel(const __grid_constant__ CUtensorMap tmS, const BpParams p)
             const float myss = -__fmul_rn(fY, k.y);
             const float ws = k.w * (1.0f / 512.0f);
             const float w256 = 512.0f * ws;
-            float4 a1, a2, b1, b2;                    // cells c (a*) and c+1 (b*), first / second float4
-            uint32_t poff = 0;
+            float4 a1, a2, b1, b2;                    // FORM 0: cells c (a*) and c+1 (b*); FORM 1: even (a*) and odd (b*) cell
+            uint32_t poff = 0;                        // FORM 0: offset of the held cell c
+            uint32_t hE = 0xFFFFFFFFu, hO = 0xFFFFFFFFu;   // FORM 1: offsets of the held even / odd cells (none yet)
 #pragma unroll
             for (int t = 0; t < BP8_VT; ++t) {
                 const float fT = __fadd_rn(__fmaf_rn(__fadd_rn(fXb, (float)t), k.x, myss), k.z);
@@ -150,25 +157,37 @@ bp8_kernel(const __grid_constant__ CUtensorMap tmS, const BpParams p)
                 const float al = __int_as_float((int)((u & 0x1FEu) | 0x4B000000u)) - 8388608.0f;
                 const float w1 = al * ws;
                 const float w0 = fmaf(-al, ws, w256);
-                const uint32_t ad = base + off;
-                if (t == 0) {
-                    a1 = lds128(ad + o1); a2 = lds128(ad + o2);
-                    b1 = lds128(ad + 128u + o1); b2 = lds128(ad + 128u + o2);
-                } else if (off != poff) {
-                    if (off == poff + 128u) {                        // moved one cell up: old c+1 is the new c
-                        a1 = b1; a2 = b2;
-                        b1 = lds128(ad + 128u + o1); b2 = lds128(ad + 128u + o2);
-                    } else if (off + 128u == poff) {                 // moved one cell down: old c is the new c+1
-                        b1 = a1; b2 = a2;
-                        a1 = lds128(ad + o1); a2 = lds128(ad + o2);
-                    } else {                                         // cannot happen for |sc| <= 1; kept for safety
+                if (FORM == 0) {
+                    const uint32_t ad = base + off;
+                    if (t == 0) {
                         a1 = lds128(ad + o1); a2 = lds128(ad + o2);
                         b1 = lds128(ad + 128u + o1); b2 = lds128(ad + 128u + o2);
+                    } else if (off != poff) {
+                        if (off == poff + 128u) {                    // moved one cell up: old c+1 is the new c
+                            a1 = b1; a2 = b2;
+                            b1 = lds128(ad + 128u + o1); b2 = lds128(ad + 128u + o2);
+                        } else if (off + 128u == poff) {             // moved one cell down: old c is the new c+1
+                            b1 = a1; b2 = a2;
+                            a1 = lds128(ad + o1); a2 = lds128(ad + o2);
+                        } else {                                     // cannot happen for |sc| <= 1; kept for safety
+                            a1 = lds128(ad + o1); a2 = lds128(ad + o2);
+                            b1 = lds128(ad + 128u + o1); b2 = lds128(ad + 128u + o2);
+                        }
                     }
+                    poff = off;
+                    acc1[t].fma(w0, a1); acc1[t].fma(w1, b1);        // acc = fmaf(w1, v1, fmaf(w0, v0, acc))
+                    acc2[t].fma(w0, a2); acc2[t].fma(w1, b2);
+                } else {
+                    // cells c and c+1 (window-relative byte offsets off, off+128): one of them is even, one odd
+                    const bool codd = (off & 128u) != 0u;
+                    const uint32_t offE = (off + 128u) & ~128u;      // the even one of {off, off+128}
+                    const uint32_t offO = off | 128u;                // the odd one
+                    if (offE != hE) { a1 = lds128(base + offE + o1); a2 = lds128(base + offE + o2); hE = offE; }
+                    if (offO != hO) { b1 = lds128(base + offO + o1); b2 = lds128(base + offO + o2); hO = offO; }
+                    const float wE = codd ? w1 : w0, wO = codd ? w0 : w1;
+                    acc1[t].fma(wE, a1); acc1[t].fma(wO, b1);
+                    acc2[t].fma(wE, a2); acc2[t].fma(wO, b2);
                 }
-                poff = off;
-                acc1[t].fma(w0, a1); acc1[t].fma(w1, b1);            // acc = fmaf(w1, v1, fmaf(w0, v0, acc))
-                acc2[t].fma(w0, a2); acc2[t].fma(w1, b2);
             }
         }
         __syncwarp();

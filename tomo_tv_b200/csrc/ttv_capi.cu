@@ -326,7 +326,7 @@ int ttv_set_option(ttv_handle h, const char* name, int value) {
     const std::string nm = name ? name : "";
     if (nm == "fgp_tiled") e.fgp_tiled = value != 0;
     else if (nm == "bp_variant") {
-        if (value != 4 && value != 8) throw CudaError("ttv_set_option: bp_variant must be 4 (default) or 8 (experimental)");
+        if (value != 4 && value != 8 && value != 9) throw CudaError("ttv_set_option: bp_variant must be 4 (default), 8 or 9 (experimental)");
         e.bp_variant = value;
     }
     else throw CudaError("ttv_set_option: unknown option '" + nm + "'");

@@ -526,11 +526,16 @@ public:
         TTV_CUDA(cudaFuncSetAttribute(bp_kernel<BP_STEP_UPD>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)BP_SMEM));
         TTV_CUDA(cudaFuncSetAttribute(bp_kernel<BP_ADD>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)BP_SMEM));
         TTV_CUDA(cudaFuncSetAttribute(bp_kernel<BP_FUSE_UPD>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)BP_SMEM));
-        TTV_CUDA(cudaFuncSetAttribute(bp8_kernel<BP_STORE>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)BP8_SMEM));
-        TTV_CUDA(cudaFuncSetAttribute(bp8_kernel<BP_SIRT_UPD>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)BP8_SMEM));
-        TTV_CUDA(cudaFuncSetAttribute(bp8_kernel<BP_STEP_UPD>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)BP8_SMEM));
-        TTV_CUDA(cudaFuncSetAttribute(bp8_kernel<BP_ADD>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)BP8_SMEM));
-        TTV_CUDA(cudaFuncSetAttribute(bp8_kernel<BP_FUSE_UPD>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)BP8_SMEM));
+        TTV_CUDA(cudaFuncSetAttribute(bp8_kernel<BP_STORE, 0>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)BP8_SMEM));
+        TTV_CUDA(cudaFuncSetAttribute(bp8_kernel<BP_STORE, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)BP8_SMEM));
+        TTV_CUDA(cudaFuncSetAttribute(bp8_kernel<BP_SIRT_UPD, 0>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)BP8_SMEM));
+        TTV_CUDA(cudaFuncSetAttribute(bp8_kernel<BP_SIRT_UPD, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)BP8_SMEM));
+        TTV_CUDA(cudaFuncSetAttribute(bp8_kernel<BP_STEP_UPD, 0>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)BP8_SMEM));
+        TTV_CUDA(cudaFuncSetAttribute(bp8_kernel<BP_STEP_UPD, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)BP8_SMEM));
+        TTV_CUDA(cudaFuncSetAttribute(bp8_kernel<BP_ADD, 0>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)BP8_SMEM));
+        TTV_CUDA(cudaFuncSetAttribute(bp8_kernel<BP_ADD, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)BP8_SMEM));
+        TTV_CUDA(cudaFuncSetAttribute(bp8_kernel<BP_FUSE_UPD, 0>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)BP8_SMEM));
+        TTV_CUDA(cudaFuncSetAttribute(bp8_kernel<BP_FUSE_UPD, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)BP8_SMEM));
     }
 
     // c_bp_angle is one __constant__ table per device: engines with different angle sets (HAADF / chemical
@@ -574,12 +579,13 @@ public:
         bind_bp_constants();
         BpParams p; if (extra) p = *extra;
         p.N = N; p.Nd = N; p.Na = Na; p.vol = vol; p.C = C.p; p.step = step;
-        if (bp_variant == 8) {
+        if (bp_variant == 8 || bp_variant == 9) {
             // experimental variant (ttv_bp8.cuh): 32 x 24 tile, 8 slices per lane, register reuse along the voxel run
             CUtensorMap tm8 = make_tmap(sino, N, Na, zb, BP8_CW, 1);
             dim3 grid8((N + BP8_TX - 1) / BP8_TX, (N + BP8_TY - 1) / BP8_TY, zb);
             ProfScope ps(*this, PF_BP);
-            bp8_kernel<EPI><<<grid8, BP8_THREADS, BP8_SMEM, st>>>(tm8, p);
+            if (bp_variant == 8) bp8_kernel<EPI, 0><<<grid8, BP8_THREADS, BP8_SMEM, st>>>(tm8, p);
+            else bp8_kernel<EPI, 1><<<grid8, BP8_THREADS, BP8_SMEM, st>>>(tm8, p);
             TTV_LAUNCH_CHECK(); ++launches;
             return;
         }
@@ -589,7 +595,7 @@ public:
         bp_kernel<EPI><<<grid, BP_THREADS, BP_SMEM, st>>>(tmS, p);
         TTV_LAUNCH_CHECK(); ++launches;
     }
-    int bp_variant = 4;             // 4: bp_kernel (default, validated); 8: bp8_kernel (experimental, ttv_set_option)
+    int bp_variant = 4;             // 4: bp_kernel (default, validated); 8 / 9: bp8_kernel FORM 0 / 1 (experimental, ttv_set_option)
 
     double read_red(int slot) {
         double v; TTV_CUDA(cudaMemcpyAsync(&v, d_red + slot, sizeof(double), cudaMemcpyDeviceToHost, st)); sync();
