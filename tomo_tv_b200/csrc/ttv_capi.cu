@@ -325,6 +325,10 @@ int ttv_set_option(ttv_handle h, const char* name, int value) {
     Engine& e = E(h);
     const std::string nm = name ? name : "";
     if (nm == "fgp_tiled") e.fgp_tiled = value != 0;
+    else if (nm == "fp_variant") {
+        if (value != 0 && value != 1) throw CudaError("ttv_set_option: fp_variant must be 0 (default) or 1 (experimental)");
+        e.fp_variant = value;
+    }
     else if (nm == "bp_variant") {
         if (value != 4 && value != 8 && value != 9) throw CudaError("ttv_set_option: bp_variant must be 4 (default), 8 or 9 (experimental)");
         e.bp_variant = value;

@@ -518,6 +518,7 @@ public:
         TTV_CUDA(cudaDeviceGetAttribute(&optin, cudaDevAttrMaxSharedMemoryPerBlockOptin, device));
         if ((size_t)optin < fp_smem) throw CudaError("forward-projector plan needs more shared memory than the device offers");
         TTV_CUDA(cudaFuncSetAttribute(fp_kernel<EPI>, cudaFuncAttributeMaxDynamicSharedMemorySize, optin));
+        TTV_CUDA(cudaFuncSetAttribute(fp_kernel<EPI, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize, optin));
     }
     void set_fp_attrs() {
         fp_attr<FP_STORE>(); fp_attr<FP_SIRT_RES>(); fp_attr<FP_KL>(); fp_attr<FP_STORE_DIST>(); fp_attr<FP_RESID>();
@@ -568,7 +569,8 @@ public:
         p.out = out; p.b = bmeas; p.R = R.p; p.red = red; p.eps = eps;
         dim3 grid(fp_ndg, fp_ngroups, zb);
         ProfScope ps(*this, PF_FP);
-        fp_kernel<EPI><<<grid, FP_THREADS, fp_smem, st>>>(tmV, tmH, p);
+        if (fp_variant == 1) fp_kernel<EPI, 1><<<grid, FP_THREADS, fp_smem, st>>>(tmV, tmH, p);       // experimental: parity-register reuse
+        else fp_kernel<EPI><<<grid, FP_THREADS, fp_smem, st>>>(tmV, tmH, p);
         TTV_LAUNCH_CHECK(); ++launches;
     }
     template <int EPI>
@@ -595,6 +597,7 @@ public:
         bp_kernel<EPI><<<grid, BP_THREADS, BP_SMEM, st>>>(tmS, p);
         TTV_LAUNCH_CHECK(); ++launches;
     }
+    int fp_variant = 0;             // 0: default; 1: parity-register reuse (experimental, ttv_set_option)
     int bp_variant = 4;             // 4: bp_kernel (default, validated); 8 / 9: bp8_kernel FORM 0 / 1 (experimental, ttv_set_option)
 
     double read_red(int slot) {

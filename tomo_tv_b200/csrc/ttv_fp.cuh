@@ -48,7 +48,13 @@ struct FpParams {
     float eps;
 };
 
-template <int EPI>
+// REUSE = 1 (EXPERIMENTAL, ttv_set_option("fp_variant", 1); compiled, never run -- see tests/test_gpu_experimental.py):
+// "parity registers".  Neighbouring detectors of a lane are 1 .. 1.41 cells apart, so the upper cell of detector t
+// is usually the lower cell of detector t+1.  The even cell of a sample lives in vE, the odd one in vO; a cell that
+// is already held is not loaded again (on average ~1.2 instead of 2 LDS.128 per sample group) and the weights are
+// swapped by the parity of the lower cell.  The two taps are then added even-cell-first, i.e. in the other order
+// whenever the lower cell is odd: equal to within one rounding of the partial sum, not bit-identical.
+template <int EPI, int REUSE = 0>
 __global__ void __launch_bounds__(FP_THREADS, 1)
 fp_kernel(const __grid_constant__ CUtensorMap tmV, const __grid_constant__ CUtensorMap tmH, const FpParams p)
 {
@@ -156,6 +162,8 @@ fp_kernel(const __grid_constant__ CUtensorMap tmV, const __grid_constant__ CUten
 #pragma unroll
                 for (int t = 0; t < FP_RT; ++t) fP[t] = __fadd_rn(fP[t], step);
             }
+            float4 vE, vO;                                            // REUSE: held even / odd cell of this line
+            uint32_t hE = 0xFFFFFFFFu, hO = 0xFFFFFFFFu;              // and their window-relative offsets (none yet)
 #pragma unroll
             for (int t = 0; t < FP_RT; ++t) {
                 const float tt = __fmaf_rd(fP[t], 256.0f, Cl);
@@ -163,10 +171,20 @@ fp_kernel(const __grid_constant__ CUtensorMap tmV, const __grid_constant__ CUten
                 const uint32_t off = (u >> 9) << 7;
                 const float w1 = __int_as_float((int)((u & 0x1FEu) | 0x4B000000u)) - 8388608.0f;   // 512*alpha
                 const float w0 = 512.0f - w1;
-                const float4 v0 = lds128(base + off);
-                const float4 v1 = lds128(base + off + 128u);
-                acc[t].fma(w0, v0);          // acc = fmaf(w1, v1, fmaf(w0, v0, acc)), 4 FFMA2
-                acc[t].fma(w1, v1);
+                if (REUSE == 0) {
+                    const float4 v0 = lds128(base + off);
+                    const float4 v1 = lds128(base + off + 128u);
+                    acc[t].fma(w0, v0);      // acc = fmaf(w1, v1, fmaf(w0, v0, acc)), 4 FFMA2
+                    acc[t].fma(w1, v1);
+                } else {
+                    const bool codd = (off & 128u) != 0u;             // cells off, off+128: one even, one odd
+                    const uint32_t offE = (off + 128u) & ~128u, offO = off | 128u;
+                    if (offE != hE) { vE = lds128(base + offE); hE = offE; }
+                    if (offO != hO) { vO = lds128(base + offO); hO = offO; }
+                    const float wE = codd ? w1 : w0, wO = codd ? w0 : w1;
+                    acc[t].fma(wE, vE);
+                    acc[t].fma(wO, vO);
+                }
             }
         }
         __syncwarp();
