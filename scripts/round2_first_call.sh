@@ -18,3 +18,5 @@ cut -c1-200 gpurun_out/r2a_bench_algos.jsonl
 # experimental kernels in their own process (a faulting kernel must not take the main suite down)
 TTV_EXPERIMENTAL=1 timeout -k 10 600 python -m pytest tests/test_gpu_experimental.py -m gpu -q --timeout 300 > gpurun_out/r2a_pytest_experimental.log 2>&1; echo "experimental exit $?"
 tail -n 15 gpurun_out/r2a_pytest_experimental.log | cut -c1-300
+# how fast are the experimental projector variants (only meaningful if the experimental tests above passed)
+timeout -k 10 900 python scripts/variants_probe.py > gpurun_out/r2a_variants.log 2>&1; cat gpurun_out/r2a_variants.log
