@@ -20,7 +20,8 @@ V, S, samples = eng.sizes()
 print(f"{opt}={val} {kern:8s} {ms:8.3f} ms  {samples / ms / 1e9:7.2f} Tsamples/s", flush=True)
 """ % ROOT
 
-n, nx, na, reps = (sys.argv[1:5] + ["512", "512", "180", "5"][len(sys.argv) - 1:])[:4] if len(sys.argv) > 1 else ("512", "512", "180", "5")
+_a = sys.argv[1:5]
+n, nx, na, reps = _a + ["512", "512", "180", "5"][len(_a):]
 for opt, val, kern in (("fp_variant", 0, "fp_sirt"), ("fp_variant", 1, "fp_sirt"),
                        ("bp_variant", 4, "bp_sirt"), ("bp_variant", 8, "bp_sirt"), ("bp_variant", 9, "bp_sirt")):
     try:
