@@ -86,3 +86,29 @@ def test_tomogpu_get_projections_inverts_the_packing(ttv):
     assert np.array_equal(t.get_projections(), ts)
     with pytest.raises(RuntimeError):
         t.show_recon()
+
+
+def test_parity_register_offsets_of_the_experimental_projector_variants():
+    """Integer bookkeeping of ttv_bp8.cuh FORM 1 / fp_kernel REUSE = 1, restated in numpy: for the cell pair
+    (c, c+1) at byte offsets (off, off+128), offE = (off+128) & ~128 is the even cell, offO = off | 128 the odd
+    one, and the weight of the lower cell goes to whichever register holds it."""
+    c = np.arange(0, 300, dtype=np.uint32)
+    off = c << 7
+    offE, offO = (off + 128) & ~np.uint32(128), off | np.uint32(128)
+    assert np.array_equal(np.sort(np.stack([offE, offO]), axis=0), np.stack([off, off + 128]))
+    assert np.all((offE >> 7) % 2 == 0) and np.all((offO >> 7) % 2 == 1)
+    codd = (off & 128) != 0
+    w0, w1 = 0.25, 0.75                                      # lower / upper cell weights
+    wE, wO = np.where(codd, w1, w0), np.where(codd, w0, w1)
+    assert np.all(np.where(offE == off, wE, wO) == w0) and np.all(np.where(offE == off + 128, wE, wO) == w1)
+    # walking a run of cells with steps of 0, +1, -1 or +2 cells reloads exactly the cells not already held
+    rng = np.random.default_rng(0)
+    cells = np.cumsum(rng.choice([0, 1, 1, 2, -1], size=200)) + 50
+    hE = hO = -1
+    loads = 0
+    for cc in cells:
+        e, o = (cc if cc % 2 == 0 else cc + 1), (cc if cc % 2 == 1 else cc + 1)
+        loads += (e != hE) + (o != hO)
+        hE, hO = e, o
+        assert {hE, hO} == {cc, cc + 1}
+    assert loads < 2 * len(cells)
