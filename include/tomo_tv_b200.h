@@ -194,7 +194,10 @@ int ttv_profile_get(ttv_handle h, const char* group, double* total_ms, long long
 /* CUDA events on the engine's stream around an arbitrary sequence of calls */
 int ttv_timer_start(ttv_handle h);
 int ttv_timer_stop(ttv_handle h, float* ms);
-/* implementation switches for A/B tests: "fgp_tiled" (1 = TMA-tiled TV-FGP sweep, 0 = first-generation kernel) */
+/* implementation switches for A/B tests: "fgp_tiled" (1 = TMA-tiled TV-FGP sweep, 0 = first-generation kernel);
+ * "fp_variant" (0 = default, 1 = experimental parity-register reuse) and "bp_variant" (4 = default, 8 / 9 =
+ * experimental 8-slices-per-lane kernels with register reuse): experimental values are not validated yet and
+ * are never selected by default. */
 int ttv_set_option(ttv_handle h, const char* name, int value);
 /* number of kernel launches issued by this engine so far */
 int ttv_launch_count(ttv_handle h, long long* n);
