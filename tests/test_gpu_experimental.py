@@ -43,7 +43,7 @@ def test_bp_variant_8_matches_default(ttv, nx, n, na):
 
 
 @pytest.mark.parametrize("nx,n,na", [(5, 40, 7), (33, 72, 17), (64, 128, 40), (40, 200, 24), (3, 512, 12)])
-def test_fp_variant_1_matches_default(ttv, nx, n, na):
+def test_fp_variants_match_default(ttv, nx, n, na):
     """fp_kernel<EPI, REUSE = 1> (parity registers: a held cell is not loaded again) adds the two taps of a sample
     even-cell-first, so it agrees with the default kernel to one rounding per sample, not bit-exactly."""
     rng = np.random.default_rng(nx * 11 + n)
@@ -51,7 +51,7 @@ def test_fp_variant_1_matches_default(ttv, nx, n, na):
     vol = rng.random((nx, n, n), dtype=np.float32)
     b = rng.random((nx, na * n), dtype=np.float32) * 3
     outs = []
-    for variant in (0, 1):
+    for variant in (0, 1, 8):
         eng = ttv.tomoengine(nx, n, ang)
         eng.set_option("fp_variant", variant)
         eng.initialize_initial_volume()
@@ -59,6 +59,7 @@ def test_fp_variant_1_matches_default(ttv, nx, n, na):
         g = eng.get_model_projections()
         eng.set_tilt_series(b); eng.initialize_SIRT(); eng.initialize_FP(); eng.restart_recon(); eng.SIRT(3)
         outs.append((g, eng.get_recon_all(), eng.data_distance()))
-    for a, c in zip(outs[0][:2], outs[1][:2]):
-        assert np.linalg.norm((a - c).ravel()) <= 1e-6 * np.linalg.norm(a.ravel())
-    assert abs(outs[0][2] - outs[1][2]) <= 1e-5 * abs(outs[0][2])
+    for other in outs[1:]:                 # variant 1 (same layout, reuse) and variant 8 (fp8_kernel: 8 slices per lane)
+        for a, c in zip(outs[0][:2], other[:2]):
+            assert np.linalg.norm((a - c).ravel()) <= 1e-6 * np.linalg.norm(a.ravel())
+        assert abs(outs[0][2] - other[2]) <= 1e-5 * abs(outs[0][2])

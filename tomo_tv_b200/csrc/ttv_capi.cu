@@ -326,7 +326,7 @@ int ttv_set_option(ttv_handle h, const char* name, int value) {
     const std::string nm = name ? name : "";
     if (nm == "fgp_tiled") e.fgp_tiled = value != 0;
     else if (nm == "fp_variant") {
-        if (value != 0 && value != 1) throw CudaError("ttv_set_option: fp_variant must be 0 (default) or 1 (experimental)");
+        if (value != 0 && value != 1 && value != 8) throw CudaError("ttv_set_option: fp_variant must be 0 (default), 1 or 8 (experimental)");
         e.fp_variant = value;
     }
     else if (nm == "bp_variant") {

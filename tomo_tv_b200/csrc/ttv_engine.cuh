@@ -8,6 +8,7 @@
 #pragma once
 #include "ttv_common.cuh"
 #include "ttv_fp.cuh"
+#include "ttv_fp8.cuh"
 #include "ttv_bp.cuh"
 #include "ttv_bp8.cuh"
 #include "ttv_tv.cuh"
@@ -519,6 +520,7 @@ public:
         if ((size_t)optin < fp_smem) throw CudaError("forward-projector plan needs more shared memory than the device offers");
         TTV_CUDA(cudaFuncSetAttribute(fp_kernel<EPI>, cudaFuncAttributeMaxDynamicSharedMemorySize, optin));
         TTV_CUDA(cudaFuncSetAttribute(fp_kernel<EPI, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize, optin));
+        TTV_CUDA(cudaFuncSetAttribute(fp8_kernel<EPI>, cudaFuncAttributeMaxDynamicSharedMemorySize, optin));
     }
     void set_fp_attrs() {
         fp_attr<FP_STORE>(); fp_attr<FP_SIRT_RES>(); fp_attr<FP_KL>(); fp_attr<FP_STORE_DIST>(); fp_attr<FP_RESID>();
@@ -570,6 +572,7 @@ public:
         dim3 grid(fp_ndg, fp_ngroups, zb);
         ProfScope ps(*this, PF_FP);
         if (fp_variant == 1) fp_kernel<EPI, 1><<<grid, FP_THREADS, fp_smem, st>>>(tmV, tmH, p);       // experimental: parity-register reuse
+        else if (fp_variant == 8) fp8_kernel<EPI><<<grid, FP8_THREADS, fp_smem, st>>>(tmV, tmH, p);    // experimental: 8 slices per lane + reuse
         else fp_kernel<EPI><<<grid, FP_THREADS, fp_smem, st>>>(tmV, tmH, p);
         TTV_LAUNCH_CHECK(); ++launches;
     }
@@ -597,7 +600,7 @@ public:
         bp_kernel<EPI><<<grid, BP_THREADS, BP_SMEM, st>>>(tmS, p);
         TTV_LAUNCH_CHECK(); ++launches;
     }
-    int fp_variant = 0;             // 0: default; 1: parity-register reuse (experimental, ttv_set_option)
+    int fp_variant = 0;             // 0: default; 1: parity-register reuse; 8: fp8_kernel (both experimental, ttv_set_option)
     int bp_variant = 4;             // 4: bp_kernel (default, validated); 8 / 9: bp8_kernel FORM 0 / 1 (experimental, ttv_set_option)
 
     double read_red(int slot) {
