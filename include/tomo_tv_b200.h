@@ -195,7 +195,7 @@ int ttv_profile_get(ttv_handle h, const char* group, double* total_ms, long long
 int ttv_timer_start(ttv_handle h);
 int ttv_timer_stop(ttv_handle h, float* ms);
 /* implementation switches for A/B tests: "fgp_tiled" (1 = TMA-tiled TV-FGP sweep, 0 = first-generation kernel);
- * "fp_variant" (0 = default, 1 = experimental parity-register reuse, 8 = experimental 8-slices-per-lane kernel) and "bp_variant" (4 = default, 8 / 9 =
+ * "fp_variant" (0 = default, 1 = experimental parity-register reuse, 8 = experimental 8-slices-per-lane kernel) and "bp_variant" (4 = default, 5 / 8 / 9 =
  * experimental 8-slices-per-lane kernels with register reuse): experimental values are not validated yet and
  * are never selected by default. */
 int ttv_set_option(ttv_handle h, const char* name, int value);

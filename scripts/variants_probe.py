@@ -23,7 +23,7 @@ print(f"{opt}={val} {kern:8s} {ms:8.3f} ms  {samples / ms / 1e9:7.2f} Tsamples/s
 _a = sys.argv[1:5]
 n, nx, na, reps = _a + ["512", "512", "180", "5"][len(_a):]
 for opt, val, kern in (("fp_variant", 0, "fp_sirt"), ("fp_variant", 1, "fp_sirt"), ("fp_variant", 8, "fp_sirt"),
-                       ("bp_variant", 4, "bp_sirt"), ("bp_variant", 8, "bp_sirt"), ("bp_variant", 9, "bp_sirt")):
+                       ("bp_variant", 4, "bp_sirt"), ("bp_variant", 5, "bp_sirt"), ("bp_variant", 8, "bp_sirt"), ("bp_variant", 9, "bp_sirt")):
     try:
         r = subprocess.run([sys.executable, "-c", CHILD, opt, str(val), kern, n, nx, na, reps], capture_output=True, text=True, timeout=300)
         print(r.stdout.strip() or f"{opt}={val}: exit {r.returncode}: {r.stderr.strip()[-300:]}", flush=True)

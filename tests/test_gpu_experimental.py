@@ -21,7 +21,7 @@ def test_bp_variant_8_matches_default(ttv, nx, n, na):
     sino = rng.standard_normal((nx, na * n)).astype(np.float32)
     b = rng.random((nx, na * n), dtype=np.float32) * 3
     outs = []
-    for variant in (4, 8, 9):
+    for variant in (4, 8, 9, 5):
         eng = ttv.tomoengine(nx, n, ang)
         eng.set_option("bp_variant", variant)
         eng.initialize_initial_volume()
@@ -37,9 +37,11 @@ def test_bp_variant_8_matches_default(ttv, nx, n, na):
         assert np.array_equal(a, c)
     assert outs[0][3] == outs[1][3]
     # variant 9 (parity registers) adds the two taps of a sample even-cell-first: one rounding of the partial sum
-    for a, c in zip(outs[0][:3], outs[2][:3]):
-        assert np.linalg.norm((a - c).ravel()) <= 1e-6 * np.linalg.norm(a.ravel())
-    assert np.allclose(outs[0][3], outs[2][3], rtol=1e-5)
+    # (so does variant 5, the same reuse inside bp_kernel's own 4-slices-per-lane layout)
+    for other in outs[2:]:
+        for a, c in zip(outs[0][:3], other[:3]):
+            assert np.linalg.norm((a - c).ravel()) <= 1e-6 * np.linalg.norm(a.ravel())
+        assert np.allclose(outs[0][3], other[3], rtol=1e-5)
 
 
 @pytest.mark.parametrize("nx,n,na", [(5, 40, 7), (33, 72, 17), (64, 128, 40), (40, 200, 24), (3, 512, 12)])

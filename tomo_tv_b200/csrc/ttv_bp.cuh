@@ -46,7 +46,11 @@ struct BpParams {
     float gamma = 1.f, lamH = 0.f;
 };
 
-template <int EPI>
+// REUSE = 1 (EXPERIMENTAL, ttv_set_option("bp_variant", 5); compiled, never run -- tests/test_gpu_experimental.py):
+// parity registers as in ttv_bp8.cuh FORM 1 inside this kernel's layout (4 slices per lane): consecutive voxels
+// of a lane are |sc| <= 1 cells apart, so a held cell is not loaded again (~6.5 instead of 16 LDS.128 per 8
+// voxels); the two taps are added even-cell-first (one rounding per sample from the default order).
+template <int EPI, int REUSE = 0>
 __global__ void __launch_bounds__(BP_THREADS, 2)
 bp_kernel(const __grid_constant__ CUtensorMap tmS, const BpParams p)
 {
@@ -120,6 +124,8 @@ bp_kernel(const __grid_constant__ CUtensorMap tmS, const BpParams p)
             const float myss = -__fmul_rn(fY, k.y);
             const float ws = k.w * (1.0f / 512.0f);
             const float w256 = 512.0f * ws;
+            float4 vE, vO;                                            // REUSE: held even / odd cell of this angle's window
+            uint32_t hE = 0xFFFFFFFFu, hO = 0xFFFFFFFFu;
 #pragma unroll
             for (int t = 0; t < BP_VT; ++t) {
                 const float fT = __fadd_rn(__fmaf_rn(fX[t], k.x, myss), k.z);
@@ -129,10 +135,20 @@ bp_kernel(const __grid_constant__ CUtensorMap tmS, const BpParams p)
                 const float al = __int_as_float((int)((u & 0x1FEu) | 0x4B000000u)) - 8388608.0f;
                 const float w1 = al * ws;
                 const float w0 = fmaf(-al, ws, w256);
-                const float4 v0 = lds128(base + off);
-                const float4 v1 = lds128(base + off + 128u);
-                acc[t].fma(w0, v0);          // acc = fmaf(w1, v1, fmaf(w0, v0, acc)), 4 FFMA2
-                acc[t].fma(w1, v1);
+                if (REUSE == 0) {
+                    const float4 v0 = lds128(base + off);
+                    const float4 v1 = lds128(base + off + 128u);
+                    acc[t].fma(w0, v0);      // acc = fmaf(w1, v1, fmaf(w0, v0, acc)), 4 FFMA2
+                    acc[t].fma(w1, v1);
+                } else {
+                    const bool codd = (off & 128u) != 0u;             // cells off, off+128: one even, one odd
+                    const uint32_t offE = (off + 128u) & ~128u, offO = off | 128u;
+                    if (offE != hE) { vE = lds128(base + offE); hE = offE; }
+                    if (offO != hO) { vO = lds128(base + offO); hO = offO; }
+                    const float wE = codd ? w1 : w0, wO = codd ? w0 : w1;
+                    acc[t].fma(wE, vE);
+                    acc[t].fma(wO, vO);
+                }
             }
         }
         __syncwarp();

@@ -330,7 +330,7 @@ int ttv_set_option(ttv_handle h, const char* name, int value) {
         e.fp_variant = value;
     }
     else if (nm == "bp_variant") {
-        if (value != 4 && value != 8 && value != 9) throw CudaError("ttv_set_option: bp_variant must be 4 (default), 8 or 9 (experimental)");
+        if (value != 4 && value != 5 && value != 8 && value != 9) throw CudaError("ttv_set_option: bp_variant must be 4 (default), 5, 8 or 9 (experimental)");
         e.bp_variant = value;
     }
     else throw CudaError("ttv_set_option: unknown option '" + nm + "'");

@@ -525,10 +525,15 @@ public:
     void set_fp_attrs() {
         fp_attr<FP_STORE>(); fp_attr<FP_SIRT_RES>(); fp_attr<FP_KL>(); fp_attr<FP_STORE_DIST>(); fp_attr<FP_RESID>();
         TTV_CUDA(cudaFuncSetAttribute(bp_kernel<BP_STORE>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)BP_SMEM));
+        TTV_CUDA(cudaFuncSetAttribute(bp_kernel<BP_STORE, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)BP_SMEM));
         TTV_CUDA(cudaFuncSetAttribute(bp_kernel<BP_SIRT_UPD>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)BP_SMEM));
+        TTV_CUDA(cudaFuncSetAttribute(bp_kernel<BP_SIRT_UPD, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)BP_SMEM));
         TTV_CUDA(cudaFuncSetAttribute(bp_kernel<BP_STEP_UPD>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)BP_SMEM));
+        TTV_CUDA(cudaFuncSetAttribute(bp_kernel<BP_STEP_UPD, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)BP_SMEM));
         TTV_CUDA(cudaFuncSetAttribute(bp_kernel<BP_ADD>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)BP_SMEM));
+        TTV_CUDA(cudaFuncSetAttribute(bp_kernel<BP_ADD, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)BP_SMEM));
         TTV_CUDA(cudaFuncSetAttribute(bp_kernel<BP_FUSE_UPD>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)BP_SMEM));
+        TTV_CUDA(cudaFuncSetAttribute(bp_kernel<BP_FUSE_UPD, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)BP_SMEM));
         TTV_CUDA(cudaFuncSetAttribute(bp8_kernel<BP_STORE, 0>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)BP8_SMEM));
         TTV_CUDA(cudaFuncSetAttribute(bp8_kernel<BP_STORE, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)BP8_SMEM));
         TTV_CUDA(cudaFuncSetAttribute(bp8_kernel<BP_SIRT_UPD, 0>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)BP8_SMEM));
@@ -597,11 +602,12 @@ public:
         const int nt = (N + BP_TILE - 1) / BP_TILE;
         dim3 grid(nt, nt, zb);
         ProfScope ps(*this, PF_BP);
-        bp_kernel<EPI><<<grid, BP_THREADS, BP_SMEM, st>>>(tmS, p);
+        if (bp_variant == 5) bp_kernel<EPI, 1><<<grid, BP_THREADS, BP_SMEM, st>>>(tmS, p);       // experimental: parity-register reuse
+        else bp_kernel<EPI><<<grid, BP_THREADS, BP_SMEM, st>>>(tmS, p);
         TTV_LAUNCH_CHECK(); ++launches;
     }
     int fp_variant = 0;             // 0: default; 1: parity-register reuse; 8: fp8_kernel (both experimental, ttv_set_option)
-    int bp_variant = 4;             // 4: bp_kernel (default, validated); 8 / 9: bp8_kernel FORM 0 / 1 (experimental, ttv_set_option)
+    int bp_variant = 4;             // 4: bp_kernel (default, validated); 5: bp_kernel with parity-register reuse; 8 / 9: bp8_kernel FORM 0 / 1 (experimental)
 
     double read_red(int slot) {
         double v; TTV_CUDA(cudaMemcpyAsync(&v, d_red + slot, sizeof(double), cudaMemcpyDeviceToHost, st)); sync();
