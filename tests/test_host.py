@@ -112,3 +112,28 @@ def test_parity_register_offsets_of_the_experimental_projector_variants():
         hE, hO = e, o
         assert {hE, hO} == {cc, cc + 1}
     assert loads < 2 * len(cells)
+
+
+def test_result_files_follow_the_reference_tree(ttv, tmp_path, monkeypatch):
+    """pytvlib.save_results / save_recon (tomofusion/pytvlib.py:120-162): /parameters attributes, /results datasets,
+    /Reconstruction/recon + size attributes -- HDF5 with h5py, the same tree as .npz keys without it."""
+    monkeypatch.chdir(tmp_path)
+    P = ttv.pytvlib
+
+    class T:
+        def get_recon(self, s):
+            return np.full((4, 4), float(s), np.float32)
+
+    path = P.save_results(("run1", "fista"), {"lambda": 0.1, "Niter": 5}, {"cost": np.arange(5.0), "tv": [1, 2, 3]})
+    assert P.save_recon(("run1", "fista"), (3, 4, 7), T()) == path
+    if path.endswith(".npz"):
+        d = np.load(path)
+        assert float(d["parameters@lambda"]) == 0.1 and int(d["parameters@Niter"]) == 5
+        assert d["results/cost"].dtype == np.float32 and np.array_equal(d["results/tv"], [1, 2, 3])
+        assert d["Reconstruction/recon"].shape == (3, 4, 4) and d["Reconstruction/recon"][2, 0, 0] == 2.0
+        assert int(d["Reconstruction@Nproj"]) == 7
+    else:
+        import h5py
+        with h5py.File(path, "r") as h5:
+            assert h5["parameters"].attrs["lambda"] == 0.1 and h5["results/cost"].dtype == np.float32
+            assert h5["Reconstruction/recon"].shape == (3, 4, 4) and h5["Reconstruction"].attrs["Nproj"] == 7
