@@ -15,8 +15,10 @@ rm -f gpurun_out/r2a_full.ncu-rep
 # secondary workloads (SIRT, SART pass, KL, CGLS, ASD-POCS iteration, FBP): first measurements of the non-headline paths
 timeout -k 10 600 python scripts/bench_algos.py --steps 3 > gpurun_out/r2a_bench_algos.jsonl 2> gpurun_out/r2a_bench_algos.err; echo "bench_algos exit $?"
 cut -c1-200 gpurun_out/r2a_bench_algos.jsonl
-# experimental kernels in their own process (a faulting kernel must not take the main suite down)
-TTV_EXPERIMENTAL=1 timeout -k 10 600 python -m pytest tests/test_gpu_experimental.py -m gpu -q --timeout 300 > gpurun_out/r2a_pytest_experimental.log 2>&1; echo "experimental exit $?"
-tail -n 15 gpurun_out/r2a_pytest_experimental.log | cut -c1-300
+# experimental kernels, one variant per process (a faulting kernel must not take the others or the main suite down)
+for v in fp1 fp8 bp5 bp8 bp9; do
+  TTV_EXPERIMENTAL=1 timeout -k 10 300 python -m pytest tests/test_gpu_experimental.py -m gpu -q --timeout 200 -k $v > gpurun_out/r2a_pytest_exp_$v.log 2>&1; echo "experimental $v exit $?"
+  tail -n 4 gpurun_out/r2a_pytest_exp_$v.log | cut -c1-300
+done
 # how fast are the experimental projector variants (only meaningful if the experimental tests above passed)
 timeout -k 10 900 python scripts/variants_probe.py > gpurun_out/r2a_variants.log 2>&1; cat gpurun_out/r2a_variants.log

@@ -1,7 +1,7 @@
 // EXPERIMENTAL back projector variant: 8 slices per lane + register reuse along the
 // voxel run.  NOT the default: selected with ttv_set_option("bp_variant", 8); written at the end of round 1
 // without GPU access, so it has compiled but never run -- the parity tests take it through
-// tests/test_gpu_parity.py::test_bp_variant_8_matches_default, which must pass before it becomes the default.
+// tests/test_gpu_experimental.py (one variant per process), which must pass before it becomes the default.
 //
 // Same arithmetic as bp_kernel (ttv_bp.cuh; reference devBP, A/cuda/2d/par_bp.cu:52-87): identical position,
 // 8-bit weight emulation and FMA order per sample, so results are bit-identical to bp_kernel.  What changes:
