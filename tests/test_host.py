@@ -137,3 +137,45 @@ def test_result_files_follow_the_reference_tree(ttv, tmp_path, monkeypatch):
         with h5py.File(path, "r") as h5:
             assert h5["parameters"].attrs["lambda"] == 0.1 and h5["results/cost"].dtype == np.float32
             assert h5["Reconstruction/recon"].shape == (3, 4, 4) and h5["Reconstruction"].attrs["Nproj"] == 7
+
+
+def test_lane_mappings_of_the_experimental_projectors_cover_their_tiles_once():
+    """Index bookkeeping of ttv_bp8.cuh / ttv_fp8.cuh restated in numpy: every (row, column, slice) of a BP tile and
+    every (angle slot, detector, slice) of an FP CTA is owned by exactly one (warp, lane, t, half), and the two
+    cells a quarter warp reads with one LDS.128 never share a bank."""
+    # --- bp8_kernel: 12 warps, tile 32 (X) x 24 (Y), lane = (g = lane >> 2, lx = lane & 3), 8 voxels along X
+    TX, TY, NW, VT = 32, 24, 12, 8
+    seen = np.zeros((TY, TX, 32), int)
+    for warp in range(NW):
+        for lane in range(32):
+            g, lx = lane >> 2, lane & 3
+            slot = warp * 8 + g
+            Y, Xb, par = slot >> 2, (slot & 3) * VT, g & 1
+            o1, o2 = lx * 32 + par * 16, lx * 32 + (par ^ 1) * 16
+            for t in range(VT):
+                for o in (o1, o2):
+                    seen[Y, Xb + t, o // 4:o // 4 + 4] += 1
+    assert np.all(seen == 1)
+    # --- fp8_kernel: 8 warps x 8 slots = 8 angles x 8 detector groups of 8, same half-cell ownership
+    seen = np.zeros((8, 64, 32), int)
+    for warp in range(8):
+        for lane in range(32):
+            gq, lx = lane >> 2, lane & 3
+            slot = warp * 8 + gq
+            ai, ds, par = slot // 8, slot % 8, gq & 1
+            assert ai == warp                                   # warp-uniform angle
+            q1, q2 = lx * 32 + par * 16, lx * 32 + (par ^ 1) * 16
+            for t in range(8):
+                for q in (q1, q2):
+                    seen[ai, ds * 8 + t, q // 4:q // 4 + 4] += 1
+    assert np.all(seen == 1)
+    # --- banks: in each quarter warp (8 lanes = two slots) the first (and the second) LDS.128 touches 32 distinct banks
+    for quarter in range(4):
+        for which in (0, 1):
+            banks = []
+            for lane in range(quarter * 8, quarter * 8 + 8):
+                g, lx = lane >> 2, lane & 3
+                par = g & 1
+                o = lx * 32 + ((par if which == 0 else par ^ 1) * 16)
+                banks += [(o // 4 + i) % 32 for i in range(4)]
+            assert len(set(banks)) == 32
