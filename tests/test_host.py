@@ -179,3 +179,28 @@ def test_lane_mappings_of_the_experimental_projectors_cover_their_tiles_once():
                 o = lx * 32 + ((par if which == 0 else par ^ 1) * 16)
                 banks += [(o // 4 + i) % 32 for i in range(4)]
             assert len(set(banks)) == 32
+
+
+@pytest.mark.parametrize("tx,ty,cw", [(16, 16, 26), (32, 24, 44)])
+def test_bp_detector_windows_hold_every_sample_of_the_tile(tx, ty, cw):
+    """Window sizing of bp_kernel (16 x 16 tile, BP_CW = 26) and the experimental bp8_kernel (32 x 24, BP8_CW = 44),
+    restated from the producer code: w0 = floor(fmin - 0.5) - 1 with fmin the smallest detector coordinate of the
+    tile's corners; every voxel's cell pair (c, c+1) relative to w0 must lie inside [0, cw)."""
+    rng = np.random.default_rng(tx)
+    lo, hi = 10 ** 9, -10 ** 9
+    for n in (512, 2048, 200):
+        for _ in range(1500):
+            th = rng.uniform(0, 2 * np.pi)
+            c, s, off = np.float32(np.cos(th)), np.float32(np.sin(th)), np.float32(n / 2)
+            x0 = int(rng.integers(0, (n + tx - 1) // tx)) * tx
+            y0 = int(rng.integers(0, (n + ty - 1) // ty)) * ty
+            fx0, fy0 = np.float32(x0 - 0.5 * n + 0.5), np.float32(y0 - 0.5 * n + 0.5)
+            ax0, ax1 = fx0 * c, np.float32(fx0 + np.float32(tx - 1)) * c
+            ay0, ay1 = -fy0 * s, -np.float32(fy0 + np.float32(ty - 1)) * s
+            fmin = np.float32(np.float32(min(ax0, ax1) + min(ay0, ay1)) + off)
+            w0 = int(np.floor(np.float32(fmin - np.float32(0.5)))) - 1
+            fx = (np.arange(x0, x0 + tx) - 0.5 * n + 0.5)[None, :]
+            fy = (np.arange(y0, y0 + ty) - 0.5 * n + 0.5)[:, None]
+            cell = np.floor(fx * float(c) - fy * float(s) + float(off) - 0.5).astype(int) - w0
+            lo, hi = min(lo, int(cell.min())), max(hi, int(cell.max()))
+    assert lo >= 0 and hi + 1 <= cw - 2          # at least one spare cell for float32 rounding at either end
