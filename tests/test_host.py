@@ -88,26 +88,33 @@ def test_tomogpu_get_projections_inverts_the_packing(ttv):
         t.show_recon()
 
 
-def test_parity_register_offsets_of_the_experimental_projector_variants():
-    """Integer bookkeeping of ttv_bp8.cuh FORM 1 / fp_kernel REUSE = 1, restated in numpy: for the cell pair
-    (c, c+1) at byte offsets (off, off+128), offE = (off+128) & ~128 is the even cell, offO = off | 128 the odd
-    one, and the weight of the lower cell goes to whichever register holds it."""
-    c = np.arange(0, 300, dtype=np.uint32)
-    off = c << 7
-    offE, offO = (off + 128) & ~np.uint32(128), off | np.uint32(128)
-    assert np.array_equal(np.sort(np.stack([offE, offO]), axis=0), np.stack([off, off + 128]))
-    assert np.all((offE >> 7) % 2 == 0) and np.all((offO >> 7) % 2 == 1)
-    codd = (off & 128) != 0
-    w0, w1 = 0.25, 0.75                                      # lower / upper cell weights
-    wE, wO = np.where(codd, w1, w0), np.where(codd, w0, w1)
-    assert np.all(np.where(offE == off, wE, wO) == w0) and np.all(np.where(offE == off + 128, wE, wO) == w1)
+def test_parity_register_bookkeeping_of_the_table_driven_projectors():
+    """Integer bookkeeping of ttv_bpt.cuh / ttv_fpt.cuh restated in numpy: of the cell pair (c, c+1) the even cell
+    is (c+1) & ~1 and the odd one c | 1, the weight of the lower cell goes to whichever register holds it, and a run
+    that keeps the cells it already holds loads exactly the missing ones."""
+    c = np.arange(0, 300)
+    cE, cO = (c + 1) & ~1, c | 1
+    assert np.array_equal(np.sort(np.stack([cE, cO]), axis=0), np.stack([c, c + 1]))
+    assert np.all(cE % 2 == 0) and np.all(cO % 2 == 1)
+    odd = (c & 1) != 0
+    w_lo, w_hi = 0.25, 0.75
+    wE, wO = np.where(odd, w_hi, w_lo), np.where(odd, w_lo, w_hi)
+    assert np.all(np.where(cE == c, wE, wO) == w_lo) and np.all(np.where(cE == c + 1, wE, wO) == w_hi)
+    # fpt entry: [even index | odd index << 8 | weight of the even cell << 16], 0xFF = held; weights 0..256 in 1/256
+    a8 = np.arange(256)
+    for cc in (6, 7):
+        wE8 = a8 if cc & 1 else 256 - a8
+        e = ((cc + 1) & ~1) | ((cc | 1) << 8) | (wE8 << 16)
+        assert np.array_equal(e & 0xFF, np.full(256, (cc + 1) & ~1)) and np.array_equal((e >> 8) & 0xFF, np.full(256, cc | 1))
+        dec = (((e >> 16) & 0xFFFF) | 0x4B000000).astype(np.uint32).view(np.float32) - np.float32(8388608.0)
+        assert np.array_equal(dec, wE8.astype(np.float32)) and np.all(dec + (256 - dec) == 256)
     # walking a run of cells with steps of 0, +1, -1 or +2 cells reloads exactly the cells not already held
     rng = np.random.default_rng(0)
     cells = np.cumsum(rng.choice([0, 1, 1, 2, -1], size=200)) + 50
     hE = hO = -1
     loads = 0
     for cc in cells:
-        e, o = (cc if cc % 2 == 0 else cc + 1), (cc if cc % 2 == 1 else cc + 1)
+        e, o = (cc + 1) & ~1, cc | 1
         loads += (e != hE) + (o != hO)
         hE, hO = e, o
         assert {hE, hO} == {cc, cc + 1}
@@ -139,51 +146,44 @@ def test_result_files_follow_the_reference_tree(ttv, tmp_path, monkeypatch):
             assert h5["Reconstruction/recon"].shape == (3, 4, 4) and h5["Reconstruction"].attrs["Nproj"] == 7
 
 
-def test_lane_mappings_of_the_experimental_projectors_cover_their_tiles_once():
-    """Index bookkeeping of ttv_bp8.cuh / ttv_fp8.cuh restated in numpy: every (row, column, slice) of a BP tile and
-    every (angle slot, detector, slice) of an FP CTA is owned by exactly one (warp, lane, t, half), and the two
-    cells a quarter warp reads with one LDS.128 never share a bank."""
-    # --- bp8_kernel: 12 warps, tile 32 (X) x 24 (Y), lane = (g = lane >> 2, lx = lane & 3), 8 voxels along X
-    TX, TY, NW, VT = 32, 24, 12, 8
-    seen = np.zeros((TY, TX, 32), int)
+def test_lane_mappings_of_the_table_driven_projectors_cover_their_tiles_once():
+    """Index bookkeeping of ttv_bpt.cuh / ttv_fpt.cuh restated in numpy: every (row, column, slice) of a BP tile and
+    every (angle slot, detector, slice) of an FP CTA is owned by exactly one (warp, lane, t, half), every quarter warp
+    reads one full 128-byte line per LDS.128, and helper threads and consumers agree on the table addresses."""
+    # --- bpt_kernel: 16 warps = 16 runs of 8 voxels in a 16 (X) x 8 (Y) tile; 8 x-blocks of 32 slices per CTA
+    TX, TY, NW, VT, XB = 16, 8, 16, 8, 8
+    seen = np.zeros((TY, TX, XB * 32), int)
     for warp in range(NW):
+        Y, Xb = warp >> 1, (warp & 1) * VT
         for lane in range(32):
-            g, lx = lane >> 2, lane & 3
-            slot = warp * 8 + g
-            Y, Xb, par = slot >> 2, (slot & 3) * VT, g & 1
-            o1, o2 = lx * 32 + par * 16, lx * 32 + (par ^ 1) * 16
+            xa, q = (lane >> 3) * 2, lane & 7
             for t in range(VT):
-                for o in (o1, o2):
-                    seen[Y, Xb + t, o // 4:o // 4 + 4] += 1
+                for xb in (xa, xa + 1):
+                    seen[Y, Xb + t, xb * 32 + q * 4: xb * 32 + q * 4 + 4] += 1
     assert np.all(seen == 1)
-    # --- fp8_kernel: 8 warps x 8 slots = 8 angles x 8 detector groups of 8, same half-cell ownership
-    seen = np.zeros((8, 64, 32), int)
-    for warp in range(8):
+    # helper warp: entry v = i*32 + lane belongs to run v >> 3, voxel v & 7; consumers read run*8 + t
+    assert sorted(i * 32 + lane for i in range(4) for lane in range(32)) == [r * 8 + t for r in range(16) for t in range(8)]
+    for quarter in range(4):                      # LDS.128 of a quarter warp: 8 lanes x 16 B of one x-block = 32 distinct banks
+        banks = [((lane >> 3) * 2 * 21 * 128 + (lane & 7) * 16) // 4 % 32 + i for lane in range(quarter * 8, quarter * 8 + 8) for i in range(4)]
+        assert len(set(banks)) == 32
+    # --- fpt_kernel: 16 warps x 4 quarter warps = 64 runs = 8 angles x 8 detector runs of 8; 2 x-blocks per CTA
+    seen = np.zeros((8, 64, 64), int)
+    for warp in range(16):
         for lane in range(32):
-            gq, lx = lane >> 2, lane & 3
-            slot = warp * 8 + gq
-            ai, ds, par = slot // 8, slot % 8, gq & 1
-            assert ai == warp                                   # warp-uniform angle
-            q1, q2 = lx * 32 + par * 16, lx * 32 + (par ^ 1) * 16
+            run, lx = warp * 4 + (lane >> 3), lane & 7
+            ai, ds = run >> 3, run & 7
+            assert ai == warp // 2                                # warp-uniform angle
             for t in range(8):
-                for q in (q1, q2):
-                    seen[ai, ds * 8 + t, q // 4:q // 4 + 4] += 1
+                for xb in (0, 1):
+                    seen[ai, ds * 8 + t, xb * 32 + lx * 4: xb * 32 + lx * 4 + 4] += 1
     assert np.all(seen == 1)
-    # --- banks: in each quarter warp (8 lanes = two slots) the first (and the second) LDS.128 touches 32 distinct banks
-    for quarter in range(4):
-        for which in (0, 1):
-            banks = []
-            for lane in range(quarter * 8, quarter * 8 + 8):
-                g, lx = lane >> 2, lane & 3
-                par = g & 1
-                o = lx * 32 + ((par if which == 0 else par ^ 1) * 16)
-                banks += [(o // 4 + i) % 32 for i in range(4)]
-            assert len(set(banks)) == 32
+    # helper thread h = run*2 + half writes 16 bytes at h*16; the consumer of `run` reads 32 bytes at run*32
+    assert [h * 16 for h in range(128)] == [run * 32 + half * 16 for run in range(64) for half in range(2)]
 
 
-@pytest.mark.parametrize("tx,ty,cw", [(16, 16, 26), (32, 24, 44)])
+@pytest.mark.parametrize("tx,ty,cw", [(16, 16, 26), (16, 8, 21)])
 def test_bp_detector_windows_hold_every_sample_of_the_tile(tx, ty, cw):
-    """Window sizing of bp_kernel (16 x 16 tile, BP_CW = 26) and the experimental bp8_kernel (32 x 24, BP8_CW = 44),
+    """Window sizing of bp_kernel (16 x 16 tile, BP_CW = 26) and bpt_kernel (16 x 8, BPT_CW = 21),
     restated from the producer code: w0 = floor(fmin - 0.5) - 1 with fmin the smallest detector coordinate of the
     tile's corners; every voxel's cell pair (c, c+1) relative to w0 must lie inside [0, cw)."""
     rng = np.random.default_rng(tx)

@@ -46,11 +46,39 @@ struct BpParams {
     float gamma = 1.f, lamH = 0.f;
 };
 
-// REUSE = 1 (EXPERIMENTAL, ttv_set_option("bp_variant", 5); compiled, never run -- tests/test_gpu_experimental.py):
-// parity registers as in ttv_bp8.cuh FORM 1 inside this kernel's layout (4 slices per lane): consecutive voxels
-// of a lane are |sc| <= 1 cells apart, so a held cell is not loaded again (~6.5 instead of 16 LDS.128 per 8
-// voxels); the two taps are added even-cell-first (one rounding per sample from the default order).
-template <int EPI, int REUSE = 0>
+// the update that follows the back projection of one voxel (4 slices): same expressions as bp_kernel's epilogue
+template <int EPI>
+__device__ __forceinline__ float4 bp_apply(const BpParams& p, size_t o, float4 r, int Y, int X)
+{
+    const int N = p.N;
+    if (EPI == BP_STORE) return r;
+    const float4 x = *reinterpret_cast<const float4*>(p.vol + o);
+    if (EPI == BP_SIRT_UPD) {
+        const float c = p.C[(size_t)Y * N + X];
+        return make_float4(fmaxf(fmaf(c, r.x, x.x), 0.f), fmaxf(fmaf(c, r.y, x.y), 0.f),
+                           fmaxf(fmaf(c, r.z, x.z), 0.f), fmaxf(fmaf(c, r.w, x.w), 0.f));
+    } else if (EPI == BP_STEP_UPD) {
+        const float c = p.step;
+        return make_float4(fmaxf(__fsub_rn(x.x, __fmul_rn(c, r.x)), 0.f), fmaxf(__fsub_rn(x.y, __fmul_rn(c, r.y)), 0.f),
+                           fmaxf(__fsub_rn(x.z, __fmul_rn(c, r.z)), 0.f), fmaxf(__fsub_rn(x.w, __fmul_rn(c, r.w)), 0.f));
+    } else if (EPI == BP_FUSE_UPD) {
+        const float4 m = *reinterpret_cast<const float4*>(p.M + o);
+        const float4 u = *reinterpret_cast<const float4*>(p.U + o);
+        const float w = p.W[(size_t)Y * N + X];
+        const float c = p.step, g = p.gamma, lh = p.lamH, gm1 = p.gamma - 1.0f;
+        auto upd = [&](float xv, float tv, float mv, float uv) -> float {
+            float h = __fmul_rn(w, __fsub_rn(uv, mv));
+            if (g != 1.0f) h = __fmul_rn(__fmul_rn(g, powf(xv, gm1)), h);
+            return fmaxf(__fsub_rn(xv, __fsub_rn(__fmul_rn(c, tv), __fmul_rn(lh, h))), 0.f);
+        };
+        return make_float4(upd(x.x, r.x, m.x, u.x), upd(x.y, r.y, m.y, u.y), upd(x.z, r.z, m.z, u.z), upd(x.w, r.w, m.w, u.w));
+    } else {  // BP_ADD
+        const float c = p.step;
+        return make_float4(fmaf(c, r.x, x.x), fmaf(c, r.y, x.y), fmaf(c, r.z, x.z), fmaf(c, r.w, x.w));
+    }
+}
+
+template <int EPI>
 __global__ void __launch_bounds__(BP_THREADS, 2)
 bp_kernel(const __grid_constant__ CUtensorMap tmS, const BpParams p)
 {
@@ -124,8 +152,6 @@ bp_kernel(const __grid_constant__ CUtensorMap tmS, const BpParams p)
             const float myss = -__fmul_rn(fY, k.y);
             const float ws = k.w * (1.0f / 512.0f);
             const float w256 = 512.0f * ws;
-            float4 vE, vO;                                            // REUSE: held even / odd cell of this angle's window
-            uint32_t hE = 0xFFFFFFFFu, hO = 0xFFFFFFFFu;
 #pragma unroll
             for (int t = 0; t < BP_VT; ++t) {
                 const float fT = __fadd_rn(__fmaf_rn(fX[t], k.x, myss), k.z);
@@ -135,20 +161,10 @@ bp_kernel(const __grid_constant__ CUtensorMap tmS, const BpParams p)
                 const float al = __int_as_float((int)((u & 0x1FEu) | 0x4B000000u)) - 8388608.0f;
                 const float w1 = al * ws;
                 const float w0 = fmaf(-al, ws, w256);
-                if (REUSE == 0) {
-                    const float4 v0 = lds128(base + off);
-                    const float4 v1 = lds128(base + off + 128u);
-                    acc[t].fma(w0, v0);      // acc = fmaf(w1, v1, fmaf(w0, v0, acc)), 4 FFMA2
-                    acc[t].fma(w1, v1);
-                } else {
-                    const bool codd = (off & 128u) != 0u;             // cells off, off+128: one even, one odd
-                    const uint32_t offE = (off + 128u) & ~128u, offO = off | 128u;
-                    if (offE != hE) { vE = lds128(base + offE); hE = offE; }
-                    if (offO != hO) { vO = lds128(base + offO); hO = offO; }
-                    const float wE = codd ? w1 : w0, wO = codd ? w0 : w1;
-                    acc[t].fma(wE, vE);
-                    acc[t].fma(wO, vO);
-                }
+                const float4 v0 = lds128(base + off);
+                const float4 v1 = lds128(base + off + 128u);
+                acc[t].fma(w0, v0);      // acc = fmaf(w1, v1, fmaf(w0, v0, acc)), 4 FFMA2
+                acc[t].fma(w1, v1);
             }
         }
         __syncwarp();
@@ -162,34 +178,7 @@ bp_kernel(const __grid_constant__ CUtensorMap tmS, const BpParams p)
             const int X = Xb + t;
             if (X < N) {
                 const size_t o = (((size_t)xb * N + Y) * N + X) * TTV_XI + lx * 4;
-                float4 r = acc[t].get();
-                if (EPI != BP_STORE) {
-                    const float4 x = *reinterpret_cast<const float4*>(p.vol + o);
-                    if (EPI == BP_SIRT_UPD) {
-                        const float c = p.C[(size_t)Y * N + X];
-                        r = make_float4(fmaxf(fmaf(c, r.x, x.x), 0.f), fmaxf(fmaf(c, r.y, x.y), 0.f),
-                                        fmaxf(fmaf(c, r.z, x.z), 0.f), fmaxf(fmaf(c, r.w, x.w), 0.f));
-                    } else if (EPI == BP_STEP_UPD) {
-                        const float c = p.step;
-                        r = make_float4(fmaxf(__fsub_rn(x.x, __fmul_rn(c, r.x)), 0.f), fmaxf(__fsub_rn(x.y, __fmul_rn(c, r.y)), 0.f),
-                                        fmaxf(__fsub_rn(x.z, __fmul_rn(c, r.z)), 0.f), fmaxf(__fsub_rn(x.w, __fmul_rn(c, r.w)), 0.f));
-                    } else if (EPI == BP_FUSE_UPD) {
-                        // same rounding sequence as the reference's Eigen expressions (no contraction on its x86-64 build)
-                        const float4 m = *reinterpret_cast<const float4*>(p.M + o);
-                        const float4 u = *reinterpret_cast<const float4*>(p.U + o);
-                        const float w = p.W[(size_t)Y * N + X];
-                        const float c = p.step, g = p.gamma, lh = p.lamH, gm1 = p.gamma - 1.0f;
-                        auto upd = [&](float xv, float tv, float mv, float uv) -> float {
-                            float h = __fmul_rn(w, __fsub_rn(uv, mv));
-                            if (g != 1.0f) h = __fmul_rn(__fmul_rn(g, powf(xv, gm1)), h);
-                            return fmaxf(__fsub_rn(xv, __fsub_rn(__fmul_rn(c, tv), __fmul_rn(lh, h))), 0.f);
-                        };
-                        r = make_float4(upd(x.x, r.x, m.x, u.x), upd(x.y, r.y, m.y, u.y), upd(x.z, r.z, m.z, u.z), upd(x.w, r.w, m.w, u.w));
-                    } else {  // BP_ADD
-                        const float c = p.step;
-                        r = make_float4(fmaf(c, r.x, x.x), fmaf(c, r.y, x.y), fmaf(c, r.z, x.z), fmaf(c, r.w, x.w));
-                    }
-                }
+                const float4 r = bp_apply<EPI>(p, o, acc[t].get(), Y, X);
                 *reinterpret_cast<float4*>(p.vol + o) = r;
             }
         }

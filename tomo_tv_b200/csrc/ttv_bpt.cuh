@@ -1,0 +1,181 @@
+// Table-driven parallel-beam back projector: 256 slices per CTA, warp-uniform voxel runs, cells reused in
+// registers.  sm_100a.  Default back projector for slabs of >= 5 x-blocks (ttv_engine.cuh: Engine::bp).
+//
+// Arithmetic: the reference's devBP (A/cuda/2d/par_bp.cu:52-87), sample position, 8-bit texture weights and
+// per-angle scale exactly as in bp_kernel (ttv_bp.cuh); the two taps of a sample are accumulated even-cell-first
+// (bp_kernel: lower-cell-first), i.e. the result differs from bp_kernel by at most one rounding per sample.
+//
+// Why (profiles/r2b_*): bp_kernel spends 8 B of shared-memory reads and ~5.5 instructions per sample; ncu shows
+// its LDS pipe 95 % busy.  Register-reuse variants with per-lane index arithmetic halved the LDS wavefronts but
+// became issue / latency bound at the same run time.  This kernel removes both costs from the hot loop:
+//   * CTA = 8 x-blocks (256 slices) x a 16 x 8 voxel tile.  A consumer warp owns ONE run of 8 consecutive voxels
+//     and all 256 slices: lane l holds slice quad (l & 7) of x-blocks 2*(l >> 3) and 2*(l >> 3) + 1, i.e. 8 slices
+//     x 8 voxels = 64 accumulators.  Cell index, weights and the reuse pattern are therefore warp-uniform.
+//   * One helper warp evaluates, per (angle, voxel), the sample position with the reference's float32 operations
+//     ONCE per CTA (bp_kernel: once per 8 lanes per x-block, i.e. 64 times) and leaves a 16-byte table entry in
+//     shared memory: {even-cell offset, odd-cell offset, weight of the even cell, weight of the odd cell}; bit 31
+//     of an offset says "this cell is the one the run already holds".  A consumer reads the entry with one
+//     broadcast LDS.128 (one wavefront) and needs no integer or float arithmetic besides the FMAs.
+//   * "Parity registers": consecutive voxels of a run move the detector coordinate by |sc| <= 1 cell, so of the
+//     two cells (c, c+1) of a sample one is even and one is odd and each is usually the cell held from the previous
+//     voxel: a run loads 2 + 7|cos| cells instead of 16 (2.5x fewer LDS wavefronts on average).
+//   * setmaxnreg: the helper warpgroup drops to 40 registers, the four consumer warpgroups grow to 104 (640 x 96 launch registers = 512 x 104 + 128 x 40 + slack: setmaxnreg.inc can only take what .dec released).
+#pragma once
+#include "ttv_bp.cuh"
+
+namespace ttv {
+
+constexpr int BPT_XB = 8;                       // x-blocks per CTA
+constexpr int BPT_VT = 8;                       // voxels per run
+constexpr int BPT_NW = 16;                      // consumer warps = runs per tile
+constexpr int BPT_TX = 16, BPT_TY = 8;          // tile: two runs along X, eight rows
+constexpr int BPT_CW = 21;                      // detector cells per angle window: 15|sc| + 7|ss| <= 16.6 -> cells 1..19 used, one spare at either end
+constexpr int BPT_NS = 8;                       // angle slots in flight
+constexpr uint32_t BPT_XBS = BPT_CW * 128u;     // x-block stride inside a slot
+constexpr uint32_t BPT_DATA = BPT_XB * BPT_XBS;
+constexpr uint32_t BPT_TAB = BPT_NW * BPT_VT * 16u;
+constexpr uint32_t BPT_SLOT = BPT_DATA + BPT_TAB;
+constexpr int BPT_THREADS = (BPT_NW + 4) * 32;
+constexpr size_t BPT_SMEM = (size_t)BPT_NS * BPT_SLOT + 2 * BPT_NS * sizeof(uint64_t);
+
+// two predicated LDS.128 (x-blocks 2q and 2q+1 of one cell): loaded only when the entry's offset is not flagged
+// "held" (bit 31); the registers keep their values otherwise
+__device__ __forceinline__ void lds_cell_if(float4& a, float4& b, uint32_t entry_off, uint32_t lane_base) {
+    asm volatile(
+        "{\n\t.reg .pred p;\n\t.reg .u32 ad;\n\t"
+        "setp.ge.s32 p, %8, 0;\n\t"
+        "add.u32 ad, %8, %9;\n\t"
+        "@p ld.shared.v4.f32 {%0,%1,%2,%3}, [ad];\n\t"
+        "@p ld.shared.v4.f32 {%4,%5,%6,%7}, [ad+%10];\n\t}"
+        : "+f"(a.x), "+f"(a.y), "+f"(a.z), "+f"(a.w), "+f"(b.x), "+f"(b.y), "+f"(b.z), "+f"(b.w)
+        : "r"(entry_off), "r"(lane_base), "n"(BPT_XBS));
+}
+__device__ __forceinline__ uint4 lds128u(uint32_t addr) {
+    uint4 v;
+    asm volatile("ld.shared.v4.u32 {%0,%1,%2,%3}, [%4];" : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w) : "r"(addr));
+    return v;
+}
+__device__ __forceinline__ void sts128u(uint32_t addr, uint4 v) {
+    asm volatile("st.shared.v4.u32 [%0], {%1,%2,%3,%4};" ::"r"(addr), "r"(v.x), "r"(v.y), "r"(v.z), "r"(v.w) : "memory");
+}
+
+template <int EPI>
+__global__ void __launch_bounds__(BPT_THREADS, 1)
+bpt_kernel(const __grid_constant__ CUtensorMap tmS, const BpParams p, int nxb)
+{
+    extern __shared__ __align__(128) unsigned char smem_raw[];
+    uint64_t* full = reinterpret_cast<uint64_t*>(smem_raw + (size_t)BPT_NS * BPT_SLOT);
+    uint64_t* empty = full + BPT_NS;
+
+    const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+    const int N = p.N, Na = p.Na;
+    const int x0 = blockIdx.x * BPT_TX, y0 = blockIdx.y * BPT_TY, xb0 = blockIdx.z * BPT_XB;
+
+    if (tid == 0) {
+        for (int s = 0; s < BPT_NS; ++s) { mbar_init(&full[s], 1); mbar_init(&empty[s], BPT_NW); }
+        fence_barrier_init();
+    }
+    __syncthreads();
+
+    if (warp >= BPT_NW) {
+        asm volatile("setmaxnreg.dec.sync.aligned.u32 40;");
+        if (warp != BPT_NW) return;
+        // ---------------- helper warp: TMA producer + table builder ----------------
+        if (lane == 0) tma_prefetch_desc(&tmS);
+        const float fX0 = (float)x0 - 0.5f * (float)N + 0.5f;
+        const float fY0 = (float)y0 - 0.5f * (float)N + 0.5f;
+        const uint32_t s_base = smem_u32(smem_raw);
+        for (int a = 0; a < Na; ++a) {
+            const int s = a % BPT_NS;
+            if (a >= BPT_NS) mbar_wait(&empty[s], ((a / BPT_NS) - 1) & 1);
+            const float4 k = c_bp_angle[a];
+            const float ax0 = fX0 * k.x, ax1 = (fX0 + (float)(BPT_TX - 1)) * k.x;
+            const float ay0 = -fY0 * k.y, ay1 = -(fY0 + (float)(BPT_TY - 1)) * k.y;
+            const float fmin = fminf(ax0, ax1) + fminf(ay0, ay1) + k.z;
+            const int w0 = (int)floorf(fmin - 0.5f) - 1;
+            if (lane == 0) tma_load_4d(smem_raw + (size_t)s * BPT_SLOT, &tmS, &full[s], 0, w0, a, xb0);
+            const float Cl = TTV_MAGIC_C(w0);
+            const float ws = k.w * (1.0f / 512.0f);
+            const float w256 = 512.0f * ws;
+#pragma unroll
+            for (int i = 0; i < BPT_NW * BPT_VT / 32; ++i) {
+                const int v = i * 32 + lane, run = v >> 3, t = v & 7;
+                const float fX = (float)(x0 + (run & 1) * BPT_VT + t) - 0.5f * (float)N + 0.5f;
+                const float fY = (float)(y0 + (run >> 1)) - 0.5f * (float)N + 0.5f;
+                const float myss = -__fmul_rn(fY, k.y);
+                const float fT = __fadd_rn(__fmaf_rn(fX, k.x, myss), k.z);
+                const float tt = __fmaf_rd(fT, 256.0f, Cl);
+                const uint32_t u = (uint32_t)(__float_as_int(tt) - TTV_MAGIC_BITS);
+                int ci = (int)(u >> 9);
+                ci = min(max(ci, 0), BPT_CW - 2);                       // never leaves the window (margin in BPT_CW); keeps a bad geometry from faulting
+                const float al = __int_as_float((int)((u & 0x1FEu) | 0x4B000000u)) - 8388608.0f;
+                const float w1 = al * ws;
+                const float wl = fmaf(-al, ws, w256);
+                const int cE = (ci + 1) & ~1, cO = ci | 1;
+                const int cip = __shfl_up_sync(0xffffffffu, ci, 1);
+                const bool first = (t == 0);
+                const bool keepE = !first && (((cip + 1) & ~1) == cE);
+                const bool keepO = !first && ((cip | 1) == cO);
+                const bool odd = (ci & 1) != 0;
+                uint4 e;
+                e.x = (uint32_t)cE * 128u | (keepE ? 0x80000000u : 0u);
+                e.y = (uint32_t)cO * 128u | (keepO ? 0x80000000u : 0u);
+                e.z = __float_as_uint(odd ? w1 : wl);
+                e.w = __float_as_uint(odd ? wl : w1);
+                sts128u(s_base + (uint32_t)s * BPT_SLOT + BPT_DATA + (uint32_t)v * 16u, e);
+            }
+            __syncwarp();
+            if (lane == 0) mbar_arrive_expect_tx(&full[s], BPT_DATA);
+        }
+        return;
+    }
+
+    // ---------------- consumer warps: warp = run ----------------
+    asm volatile("setmaxnreg.inc.sync.aligned.u32 104;");
+    const int Y = y0 + (warp >> 1);
+    const int Xb = x0 + (warp & 1) * BPT_VT;
+    const int xbA = xb0 + (lane >> 3) * 2;
+    const uint32_t lane_off = (uint32_t)(lane >> 3) * 2u * BPT_XBS + (uint32_t)(lane & 7) * 16u;
+
+    Acc4 acc1[BPT_VT], acc2[BPT_VT];
+#pragma unroll
+    for (int t = 0; t < BPT_VT; ++t) { acc1[t].zero(); acc2[t].zero(); }
+    const uint32_t s_base = smem_u32(smem_raw);
+    float4 E1 = make_float4(0.f, 0.f, 0.f, 0.f), E2 = E1, O1 = E1, O2 = E1;
+
+#pragma unroll 1
+    for (int a = 0; a < Na; ++a) {
+        const int s = a % BPT_NS;
+        mbar_wait(&full[s], (a / BPT_NS) & 1);
+        const uint32_t slot = s_base + (uint32_t)s * BPT_SLOT;
+        const uint32_t tab = slot + BPT_DATA + (uint32_t)warp * (BPT_VT * 16u);
+        const uint32_t lb = slot + lane_off;
+#pragma unroll
+        for (int t = 0; t < BPT_VT; ++t) {
+            const uint4 e = lds128u(tab + (uint32_t)t * 16u);
+            lds_cell_if(E1, E2, e.x, lb);
+            lds_cell_if(O1, O2, e.y, lb);
+            const float wE = __uint_as_float(e.z), wO = __uint_as_float(e.w);
+            acc1[t].fma(wE, E1); acc1[t].fma(wO, O1);
+            acc2[t].fma(wE, E2); acc2[t].fma(wO, O2);
+        }
+        __syncwarp();
+        if (lane == 0) mbar_arrive(&empty[s]);
+    }
+
+    // ---------------- epilogue ----------------
+    if (Y < N) {
+#pragma unroll
+        for (int t = 0; t < BPT_VT; ++t) {
+            const int X = Xb + t;
+            if (X < N) {
+                const size_t oa = (((size_t)xbA * N + Y) * N + X) * TTV_XI + (size_t)(lane & 7) * 4;
+                const size_t ob = oa + (size_t)N * N * TTV_XI;
+                if (xbA < nxb) *reinterpret_cast<float4*>(p.vol + oa) = bp_apply<EPI>(p, oa, acc1[t].get(), Y, X);
+                if (xbA + 1 < nxb) *reinterpret_cast<float4*>(p.vol + ob) = bp_apply<EPI>(p, ob, acc2[t].get(), Y, X);
+            }
+        }
+    }
+}
+
+}  // namespace ttv

@@ -326,11 +326,11 @@ int ttv_set_option(ttv_handle h, const char* name, int value) {
     const std::string nm = name ? name : "";
     if (nm == "fgp_tiled") e.fgp_tiled = value != 0;
     else if (nm == "fp_variant") {
-        if (value != 0 && value != 1 && value != 8) throw CudaError("ttv_set_option: fp_variant must be 0 (default), 1 or 8 (experimental)");
+        if (value < 0 || value > 2) throw CudaError("ttv_set_option: fp_variant must be 0 (by slab thickness), 1 (classic) or 2 (table-driven)");
         e.fp_variant = value;
     }
     else if (nm == "bp_variant") {
-        if (value != 4 && value != 5 && value != 8 && value != 9) throw CudaError("ttv_set_option: bp_variant must be 4 (default), 5, 8 or 9 (experimental)");
+        if (value < 0 || value > 2) throw CudaError("ttv_set_option: bp_variant must be 0 (by slab thickness), 1 (classic) or 2 (table-driven)");
         e.bp_variant = value;
     }
     else throw CudaError("ttv_set_option: unknown option '" + nm + "'");

@@ -8,9 +8,9 @@
 #pragma once
 #include "ttv_common.cuh"
 #include "ttv_fp.cuh"
-#include "ttv_fp8.cuh"
+#include "ttv_fpt.cuh"
 #include "ttv_bp.cuh"
-#include "ttv_bp8.cuh"
+#include "ttv_bpt.cuh"
 #include "ttv_tv.cuh"
 #include "ttv_fgp.cuh"
 #include "ttv_elem.cuh"
@@ -41,16 +41,31 @@ inline PFN_encodeTiled get_encode_tiled() {
     return fn;
 }
 // 4-D map over an x-interleaved array [d3][d2][d1][32] of float32 with the given box.
-inline CUtensorMap make_tmap(const float* base, uint64_t d1, uint64_t d2, uint64_t d3, uint32_t b1, uint32_t b2, uint32_t b0 = 32) {
+inline CUtensorMap make_tmap(const float* base, uint64_t d1, uint64_t d2, uint64_t d3, uint32_t b1, uint32_t b2, uint32_t b0 = 32, uint32_t b3 = 1) {
     CUtensorMap tm;
     cuuint64_t dims[4] = {32, d1, d2, d3};
     cuuint64_t strides[3] = {128, 128 * d1, 128 * d1 * d2};
-    cuuint32_t box[4] = {b0, b1, b2, 1};
+    cuuint32_t box[4] = {b0, b1, b2, b3};
     cuuint32_t estr[4] = {1, 1, 1, 1};
     CUresult r = get_encode_tiled()(&tm, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 4, const_cast<float*>(base), dims, strides, box, estr,
                                     CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_NONE, CU_TENSOR_MAP_L2_PROMOTION_L2_128B,
                                     CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
     if (r != CUDA_SUCCESS) throw CudaError("cuTensorMapEncodeTiled failed (code " + std::to_string((int)r) + ")");
+    return tm;
+}
+
+// 4-D map over the same array with the x-block as SECOND dimension: (32, d3, d1, d2), box (32, bxb, b1, b2).  A box lands in
+// shared memory as [b2][b1][bxb][32], i.e. the x-blocks of one cell are adjacent (ttv_fpt.cuh).
+inline CUtensorMap make_tmap_xb(const float* base, uint64_t d1, uint64_t d2, uint64_t d3, uint32_t bxb, uint32_t b1, uint32_t b2) {
+    CUtensorMap tm;
+    cuuint64_t dims[4] = {32, d3, d1, d2};
+    cuuint64_t strides[3] = {128 * d1 * d2, 128, 128 * d1};
+    cuuint32_t box[4] = {32, bxb, b1, b2};
+    cuuint32_t estr[4] = {1, 1, 1, 1};
+    CUresult r = get_encode_tiled()(&tm, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 4, const_cast<float*>(base), dims, strides, box, estr,
+                                    CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_NONE, CU_TENSOR_MAP_L2_PROMOTION_L2_128B,
+                                    CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    if (r != CUDA_SUCCESS) throw CudaError("cuTensorMapEncodeTiled (x-block-interleaved) failed (code " + std::to_string((int)r) + ")");
     return tm;
 }
 
@@ -230,7 +245,7 @@ public:
 
     // FP plan
     int* d_win0 = nullptr; FpAngle* d_fpang = nullptr; FpGroup* d_fpgrp = nullptr;
-    int fp_ngroups = 0, fp_ndg = 0, fp_CW = 0, fp_TR = 2, fp_S = 2; size_t fp_smem = 0;
+    int fp_ngroups = 0, fp_ndg = 0, fp_CW = 0, fp_TR = 2, fp_S = 2; size_t fp_smem = 0; int fpt_NS = 0; size_t fpt_smem = 0;
     float* d_theta = nullptr;
 
     // state (x-interleaved)
@@ -498,6 +513,10 @@ public:
         int S = (int)std::min<size_t>(FP_MAX_STAGES, budget / stage_b);
         if (S < 2) throw CudaError("forward-projector stage does not fit in shared memory");
         fp_CW = CW; fp_TR = TR; fp_S = S; fp_ngroups = (int)fg.size(); fp_ndg = ndg;
+        if (CW > 254) throw CudaError("forward-projector window exceeds the table-entry range");
+        fpt_NS = (int)std::min<size_t>(FPT_MAX_SLOTS, (size_t)(220 * 1024) / fpt_slot_bytes(CW));
+        if (fpt_NS < 3) throw CudaError("forward-projector line slot does not fit in shared memory");
+        fpt_smem = (size_t)fpt_NS * fpt_slot_bytes(CW) + 2 * fpt_NS * sizeof(uint64_t);
         fp_smem = (size_t)S * stage_b + (size_t)(S * TR + 1) * sizeof(float) + 2 * S * sizeof(uint64_t) + 16;
         cudaFree(d_win0); cudaFree(d_fpang); cudaFree(d_fpgrp); cudaFree(d_theta);
         TTV_CUDA(cudaMalloc(&d_win0, win.size() * sizeof(int)));
@@ -519,31 +538,15 @@ public:
         TTV_CUDA(cudaDeviceGetAttribute(&optin, cudaDevAttrMaxSharedMemoryPerBlockOptin, device));
         if ((size_t)optin < fp_smem) throw CudaError("forward-projector plan needs more shared memory than the device offers");
         TTV_CUDA(cudaFuncSetAttribute(fp_kernel<EPI>, cudaFuncAttributeMaxDynamicSharedMemorySize, optin));
-        TTV_CUDA(cudaFuncSetAttribute(fp_kernel<EPI, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize, optin));
-        TTV_CUDA(cudaFuncSetAttribute(fp8_kernel<EPI>, cudaFuncAttributeMaxDynamicSharedMemorySize, optin));
+        TTV_CUDA(cudaFuncSetAttribute(fpt_kernel<EPI>, cudaFuncAttributeMaxDynamicSharedMemorySize, optin));
+    }
+    template <int EPI> void bp_attr() {
+        TTV_CUDA(cudaFuncSetAttribute(bp_kernel<EPI>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)BP_SMEM));
+        TTV_CUDA(cudaFuncSetAttribute(bpt_kernel<EPI>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)BPT_SMEM));
     }
     void set_fp_attrs() {
         fp_attr<FP_STORE>(); fp_attr<FP_SIRT_RES>(); fp_attr<FP_KL>(); fp_attr<FP_STORE_DIST>(); fp_attr<FP_RESID>();
-        TTV_CUDA(cudaFuncSetAttribute(bp_kernel<BP_STORE>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)BP_SMEM));
-        TTV_CUDA(cudaFuncSetAttribute(bp_kernel<BP_STORE, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)BP_SMEM));
-        TTV_CUDA(cudaFuncSetAttribute(bp_kernel<BP_SIRT_UPD>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)BP_SMEM));
-        TTV_CUDA(cudaFuncSetAttribute(bp_kernel<BP_SIRT_UPD, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)BP_SMEM));
-        TTV_CUDA(cudaFuncSetAttribute(bp_kernel<BP_STEP_UPD>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)BP_SMEM));
-        TTV_CUDA(cudaFuncSetAttribute(bp_kernel<BP_STEP_UPD, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)BP_SMEM));
-        TTV_CUDA(cudaFuncSetAttribute(bp_kernel<BP_ADD>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)BP_SMEM));
-        TTV_CUDA(cudaFuncSetAttribute(bp_kernel<BP_ADD, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)BP_SMEM));
-        TTV_CUDA(cudaFuncSetAttribute(bp_kernel<BP_FUSE_UPD>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)BP_SMEM));
-        TTV_CUDA(cudaFuncSetAttribute(bp_kernel<BP_FUSE_UPD, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)BP_SMEM));
-        TTV_CUDA(cudaFuncSetAttribute(bp8_kernel<BP_STORE, 0>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)BP8_SMEM));
-        TTV_CUDA(cudaFuncSetAttribute(bp8_kernel<BP_STORE, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)BP8_SMEM));
-        TTV_CUDA(cudaFuncSetAttribute(bp8_kernel<BP_SIRT_UPD, 0>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)BP8_SMEM));
-        TTV_CUDA(cudaFuncSetAttribute(bp8_kernel<BP_SIRT_UPD, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)BP8_SMEM));
-        TTV_CUDA(cudaFuncSetAttribute(bp8_kernel<BP_STEP_UPD, 0>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)BP8_SMEM));
-        TTV_CUDA(cudaFuncSetAttribute(bp8_kernel<BP_STEP_UPD, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)BP8_SMEM));
-        TTV_CUDA(cudaFuncSetAttribute(bp8_kernel<BP_ADD, 0>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)BP8_SMEM));
-        TTV_CUDA(cudaFuncSetAttribute(bp8_kernel<BP_ADD, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)BP8_SMEM));
-        TTV_CUDA(cudaFuncSetAttribute(bp8_kernel<BP_FUSE_UPD, 0>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)BP8_SMEM));
-        TTV_CUDA(cudaFuncSetAttribute(bp8_kernel<BP_FUSE_UPD, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)BP8_SMEM));
+        bp_attr<BP_STORE>(); bp_attr<BP_SIRT_UPD>(); bp_attr<BP_STEP_UPD>(); bp_attr<BP_ADD>(); bp_attr<BP_FUSE_UPD>();
     }
 
     // c_bp_angle is one __constant__ table per device: engines with different angle sets (HAADF / chemical
@@ -568,17 +571,23 @@ public:
     void fp(const float* vol, float* out, const float* bmeas, double* red, int nblocks = -1, float eps = 0.1f) {
         need_angles();
         const int zb = nblocks < 0 ? nxb : nblocks;
-        CUtensorMap tmV = make_tmap(vol, N, N, zb, fp_CW, 1);
-        CUtensorMap tmH = make_tmap(vol, N, N, zb, 1, fp_CW);
         FpParams p;
         p.ang = d_fpang; p.grp = d_fpgrp; p.win0 = d_win0;
         p.N = N; p.Nd = N; p.Na = Na; p.ndg = fp_ndg; p.CW = fp_CW; p.TR = fp_TR; p.S = fp_S;
         p.out = out; p.b = bmeas; p.R = R.p; p.red = red; p.eps = eps;
-        dim3 grid(fp_ndg, fp_ngroups, zb);
         ProfScope ps(*this, PF_FP);
-        if (fp_variant == 1) fp_kernel<EPI, 1><<<grid, FP_THREADS, fp_smem, st>>>(tmV, tmH, p);       // experimental: parity-register reuse
-        else if (fp_variant == 8) fp8_kernel<EPI><<<grid, FP8_THREADS, fp_smem, st>>>(tmV, tmH, p);    // experimental: 8 slices per lane + reuse
-        else fp_kernel<EPI><<<grid, FP_THREADS, fp_smem, st>>>(tmV, tmH, p);
+        if (fp_variant == 2 || (fp_variant == 0 && zb >= 2)) {
+            // table-driven kernel (ttv_fpt.cuh): 2 x-blocks per CTA, one line per slot
+            CUtensorMap tmV = make_tmap_xb(vol, N, N, zb, FPT_XB, fp_CW, 1);
+            CUtensorMap tmH = make_tmap_xb(vol, N, N, zb, FPT_XB, 1, fp_CW);
+            dim3 grid(fp_ndg, fp_ngroups, (zb + FPT_XB - 1) / FPT_XB);
+            fpt_kernel<EPI><<<grid, FPT_THREADS, fpt_smem, st>>>(tmV, tmH, p, zb, fpt_NS);
+        } else {
+            CUtensorMap tmV = make_tmap(vol, N, N, zb, fp_CW, 1);
+            CUtensorMap tmH = make_tmap(vol, N, N, zb, 1, fp_CW);
+            dim3 grid(fp_ndg, fp_ngroups, zb);
+            fp_kernel<EPI><<<grid, FP_THREADS, fp_smem, st>>>(tmV, tmH, p);
+        }
         TTV_LAUNCH_CHECK(); ++launches;
     }
     template <int EPI>
@@ -589,25 +598,24 @@ public:
         bind_bp_constants();
         BpParams p; if (extra) p = *extra;
         p.N = N; p.Nd = N; p.Na = Na; p.vol = vol; p.C = C.p; p.step = step;
-        if (bp_variant == 8 || bp_variant == 9) {
-            // experimental variant (ttv_bp8.cuh): 32 x 24 tile, 8 slices per lane, register reuse along the voxel run
-            CUtensorMap tm8 = make_tmap(sino, N, Na, zb, BP8_CW, 1);
-            dim3 grid8((N + BP8_TX - 1) / BP8_TX, (N + BP8_TY - 1) / BP8_TY, zb);
+        // table-driven kernel (ttv_bpt.cuh): 8 x-blocks per CTA; the classic kernel serves thin slabs
+        if (bp_variant == 2 || (bp_variant == 0 && zb >= 5)) {
+            CUtensorMap tmT = make_tmap(sino, N, Na, zb, BPT_CW, 1, 32, BPT_XB);
+            dim3 gridT((N + BPT_TX - 1) / BPT_TX, (N + BPT_TY - 1) / BPT_TY, (zb + BPT_XB - 1) / BPT_XB);
             ProfScope ps(*this, PF_BP);
-            if (bp_variant == 8) bp8_kernel<EPI, 0><<<grid8, BP8_THREADS, BP8_SMEM, st>>>(tm8, p);
-            else bp8_kernel<EPI, 1><<<grid8, BP8_THREADS, BP8_SMEM, st>>>(tm8, p);
+            bpt_kernel<EPI><<<gridT, BPT_THREADS, BPT_SMEM, st>>>(tmT, p, zb);
             TTV_LAUNCH_CHECK(); ++launches;
             return;
         }
         const int nt = (N + BP_TILE - 1) / BP_TILE;
         dim3 grid(nt, nt, zb);
         ProfScope ps(*this, PF_BP);
-        if (bp_variant == 5) bp_kernel<EPI, 1><<<grid, BP_THREADS, BP_SMEM, st>>>(tmS, p);       // experimental: parity-register reuse
-        else bp_kernel<EPI><<<grid, BP_THREADS, BP_SMEM, st>>>(tmS, p);
+        bp_kernel<EPI><<<grid, BP_THREADS, BP_SMEM, st>>>(tmS, p);
         TTV_LAUNCH_CHECK(); ++launches;
     }
-    int fp_variant = 0;             // 0: default; 1: parity-register reuse; 8: fp8_kernel (both experimental, ttv_set_option)
-    int bp_variant = 4;             // 4: bp_kernel (default, validated); 5: bp_kernel with parity-register reuse; 8 / 9: bp8_kernel FORM 0 / 1 (experimental)
+    // projector kernel choice (ttv_set_option): 0 = by slab thickness (default), 1 = classic kernel (fp_kernel / bp_kernel),
+    // 2 = table-driven kernel (fpt_kernel / bpt_kernel) whatever the slab thickness
+    int fp_variant = 0, bp_variant = 0;
 
     double read_red(int slot) {
         double v; TTV_CUDA(cudaMemcpyAsync(&v, d_red + slot, sizeof(double), cudaMemcpyDeviceToHost, st)); sync();

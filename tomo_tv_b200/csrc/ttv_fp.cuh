@@ -48,13 +48,40 @@ struct FpParams {
     float eps;
 };
 
-// REUSE = 1 (EXPERIMENTAL, ttv_set_option("fp_variant", 1); compiled, never run -- see tests/test_gpu_experimental.py):
-// "parity registers".  Neighbouring detectors of a lane are 1 .. 1.41 cells apart, so the upper cell of detector t
-// is usually the lower cell of detector t+1.  The even cell of a sample lives in vE, the odd one in vO; a cell that
-// is already held is not loaded again (on average ~1.2 instead of 2 LDS.128 per sample group) and the weights are
-// swapped by the parity of the lower cell.  The two taps are then added even-cell-first, i.e. in the other order
-// whenever the lower cell is odd: equal to within one rounding of the partial sum, not bit-identical.
-template <int EPI, int REUSE = 0>
+// what follows the projection of one ray (4 slices, already scaled): store / SIRT residual (b-Ax)*R
+// (A/cuda/2d/sirt.cu:246-257) / KL ratio + cost (T/gpu/utils/tomoengine.cpp:301-311) / store + squared distance
+// (tomoengine.cpp:410-413) / plain residual
+template <int EPI>
+__device__ __forceinline__ void fp_emit(const FpParams& p, int orig, int d, int xb, int lx, float4 ax, float& part)
+{
+    const size_t cell = ((size_t)xb * p.Na + orig) * p.Nd + d;
+    const size_t o = cell * TTV_XI + lx * 4;
+    float4 r;
+    if (EPI == FP_STORE) {
+        r = ax;
+    } else {
+        const float4 bb = *reinterpret_cast<const float4*>(p.b + o);
+        if (EPI == FP_SIRT_RES) {
+            const float w = p.R[(size_t)orig * p.Nd + d];
+            r = make_float4((bb.x - ax.x) * w, (bb.y - ax.y) * w, (bb.z - ax.z) * w, (bb.w - ax.w) * w);
+        } else if (EPI == FP_RESID) {
+            r = make_float4(bb.x - ax.x, bb.y - ax.y, bb.z - ax.z, bb.w - ax.w);
+        } else if (EPI == FP_KL) {
+            const float e = p.eps;
+            r = make_float4((ax.x - bb.x) / (ax.x + e), (ax.y - bb.y) / (ax.y + e),
+                            (ax.z - bb.z) / (ax.z + e), (ax.w - bb.w) / (ax.w + e));
+            part += (ax.x - bb.x * logf(ax.x + e)) + (ax.y - bb.y * logf(ax.y + e))
+                  + (ax.z - bb.z * logf(ax.z + e)) + (ax.w - bb.w * logf(ax.w + e));
+        } else {  // FP_STORE_DIST
+            r = ax;
+            const float dx = ax.x - bb.x, dy = ax.y - bb.y, dz = ax.z - bb.z, dw = ax.w - bb.w;
+            part += dx * dx + dy * dy + dz * dz + dw * dw;
+        }
+    }
+    *reinterpret_cast<float4*>(p.out + o) = r;
+}
+
+template <int EPI>
 __global__ void __launch_bounds__(FP_THREADS, 1)
 fp_kernel(const __grid_constant__ CUtensorMap tmV, const __grid_constant__ CUtensorMap tmH, const FpParams p)
 {
@@ -162,8 +189,6 @@ fp_kernel(const __grid_constant__ CUtensorMap tmV, const __grid_constant__ CUten
 #pragma unroll
                 for (int t = 0; t < FP_RT; ++t) fP[t] = __fadd_rn(fP[t], step);
             }
-            float4 vE, vO;                                            // REUSE: held even / odd cell of this line
-            uint32_t hE = 0xFFFFFFFFu, hO = 0xFFFFFFFFu;              // and their window-relative offsets (none yet)
 #pragma unroll
             for (int t = 0; t < FP_RT; ++t) {
                 const float tt = __fmaf_rd(fP[t], 256.0f, Cl);
@@ -171,20 +196,10 @@ fp_kernel(const __grid_constant__ CUtensorMap tmV, const __grid_constant__ CUten
                 const uint32_t off = (u >> 9) << 7;
                 const float w1 = __int_as_float((int)((u & 0x1FEu) | 0x4B000000u)) - 8388608.0f;   // 512*alpha
                 const float w0 = 512.0f - w1;
-                if (REUSE == 0) {
-                    const float4 v0 = lds128(base + off);
-                    const float4 v1 = lds128(base + off + 128u);
-                    acc[t].fma(w0, v0);      // acc = fmaf(w1, v1, fmaf(w0, v0, acc)), 4 FFMA2
-                    acc[t].fma(w1, v1);
-                } else {
-                    const bool codd = (off & 128u) != 0u;             // cells off, off+128: one even, one odd
-                    const uint32_t offE = (off + 128u) & ~128u, offO = off | 128u;
-                    if (offE != hE) { vE = lds128(base + offE); hE = offE; }
-                    if (offO != hO) { vO = lds128(base + offO); hO = offO; }
-                    const float wE = codd ? w1 : w0, wO = codd ? w0 : w1;
-                    acc[t].fma(wE, vE);
-                    acc[t].fma(wO, vO);
-                }
+                const float4 v0 = lds128(base + off);
+                const float4 v1 = lds128(base + off + 128u);
+                acc[t].fma(w0, v0);      // acc = fmaf(w1, v1, fmaf(w0, v0, acc)), 4 FFMA2
+                acc[t].fma(w1, v1);
             }
         }
         __syncwarp();
@@ -200,33 +215,8 @@ fp_kernel(const __grid_constant__ CUtensorMap tmV, const __grid_constant__ CUten
         for (int t = 0; t < FP_RT; ++t) {
             const int d = dbase + t;
             if (d < p.Nd) {
-                const size_t cell = ((size_t)xb * p.Na + A.orig) * p.Nd + d;
-                const size_t o = cell * TTV_XI + lx * 4;
                 const float4 a4 = acc[t].get();
-                float4 ax = make_float4(a4.x * cs, a4.y * cs, a4.z * cs, a4.w * cs);
-                float4 r;
-                if (EPI == FP_STORE) {
-                    r = ax;
-                } else {
-                    const float4 bb = *reinterpret_cast<const float4*>(p.b + o);
-                    if (EPI == FP_SIRT_RES) {
-                        const float w = p.R[(size_t)A.orig * p.Nd + d];
-                        r = make_float4((bb.x - ax.x) * w, (bb.y - ax.y) * w, (bb.z - ax.z) * w, (bb.w - ax.w) * w);
-                    } else if (EPI == FP_RESID) {
-                        r = make_float4(bb.x - ax.x, bb.y - ax.y, bb.z - ax.z, bb.w - ax.w);
-                    } else if (EPI == FP_KL) {
-                        const float e = p.eps;
-                        r = make_float4((ax.x - bb.x) / (ax.x + e), (ax.y - bb.y) / (ax.y + e),
-                                        (ax.z - bb.z) / (ax.z + e), (ax.w - bb.w) / (ax.w + e));
-                        part += (ax.x - bb.x * logf(ax.x + e)) + (ax.y - bb.y * logf(ax.y + e))
-                              + (ax.z - bb.z * logf(ax.z + e)) + (ax.w - bb.w * logf(ax.w + e));
-                    } else {  // FP_STORE_DIST
-                        r = ax;
-                        const float dx = ax.x - bb.x, dy = ax.y - bb.y, dz = ax.z - bb.z, dw = ax.w - bb.w;
-                        part += dx * dx + dy * dy + dz * dz + dw * dw;
-                    }
-                }
-                *reinterpret_cast<float4*>(p.out + o) = r;
+                fp_emit<EPI>(p, A.orig, d, xb, lx, make_float4(a4.x * cs, a4.y * cs, a4.z * cs, a4.w * cs), part);
             }
         }
     }
