@@ -164,7 +164,7 @@ def test_lane_mappings_of_the_table_driven_projectors_cover_their_tiles_once():
     # helper warp: entry v = i*32 + lane belongs to run v >> 3, voxel v & 7; consumers read run*8 + t
     assert sorted(i * 32 + lane for i in range(4) for lane in range(32)) == [r * 8 + t for r in range(16) for t in range(8)]
     for quarter in range(4):                      # LDS.128 of a quarter warp: 8 lanes x 16 B of one x-block = 32 distinct banks
-        banks = [((lane >> 3) * 2 * 21 * 128 + (lane & 7) * 16) // 4 % 32 + i for lane in range(quarter * 8, quarter * 8 + 8) for i in range(4)]
+        banks = [(((lane >> 3) * 256 + (lane & 7) * 16) // 4 + i) % 32 for lane in range(quarter * 8, quarter * 8 + 8) for i in range(4)]
         assert len(set(banks)) == 32
     # --- fpt_kernel: 16 warps x 4 quarter warps = 64 runs = 8 angles x 8 detector runs of 8; 2 x-blocks per CTA
     seen = np.zeros((8, 64, 64), int)

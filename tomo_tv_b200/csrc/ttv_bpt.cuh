@@ -2,24 +2,29 @@
 // registers.  sm_100a.  Default back projector for slabs of >= 5 x-blocks (ttv_engine.cuh: Engine::bp).
 //
 // Arithmetic: the reference's devBP (A/cuda/2d/par_bp.cu:52-87), sample position, 8-bit texture weights and
-// per-angle scale exactly as in bp_kernel (ttv_bp.cuh); the two taps of a sample are accumulated even-cell-first
-// (bp_kernel: lower-cell-first), i.e. the result differs from bp_kernel by at most one rounding per sample.
+// per-angle scale as in bp_kernel (ttv_bp.cuh); the two taps of a sample are accumulated even-cell-first
+// (bp_kernel: lower-cell-first) and the weight of the even cell is one rounded product, i.e. the result differs
+// from bp_kernel's by rounding (~1e-7), not systematically.
 //
 // Why (profiles/r2b_*): bp_kernel spends 8 B of shared-memory reads and ~5.5 instructions per sample; ncu shows
 // its LDS pipe 95 % busy.  Register-reuse variants with per-lane index arithmetic halved the LDS wavefronts but
 // became issue / latency bound at the same run time.  This kernel removes both costs from the hot loop:
-//   * CTA = 8 x-blocks (256 slices) x a 16 x 8 voxel tile.  A consumer warp owns ONE run of 8 consecutive voxels
-//     and all 256 slices: lane l holds slice quad (l & 7) of x-blocks 2*(l >> 3) and 2*(l >> 3) + 1, i.e. 8 slices
-//     x 8 voxels = 64 accumulators.  Cell index, weights and the reuse pattern are therefore warp-uniform.
+//   * CTA = 8 x-blocks (256 slices) x a 16 x 8 voxel tile; staged detector cells are x-block-interleaved
+//     ([cell][xb][32], one 4-D TMA box per angle over a tensor map whose second dimension is the x-block).
+//     A consumer warp owns ONE run of 8 consecutive voxels and all 256 slices: lane l holds slice quad (l & 7)
+//     of x-blocks 2*(l >> 3) and 2*(l >> 3) + 1 (two LDS.128 128 B apart), i.e. 8 slices x 8 voxels = 64
+//     accumulators.  Cell index, weights and the reuse pattern are warp-uniform.
 //   * One helper warp evaluates, per (angle, voxel), the sample position with the reference's float32 operations
-//     ONCE per CTA (bp_kernel: once per 8 lanes per x-block, i.e. 64 times) and leaves a 16-byte table entry in
-//     shared memory: {even-cell offset, odd-cell offset, weight of the even cell, weight of the odd cell}; bit 31
-//     of an offset says "this cell is the one the run already holds".  A consumer reads the entry with one
-//     broadcast LDS.128 (one wavefront) and needs no integer or float arithmetic besides the FMAs.
+//     ONCE per CTA (bp_kernel: once per 8 lanes per x-block, i.e. 64 times) and leaves a 4-byte entry in shared
+//     memory: [even-cell index | odd-cell index | weight of the even cell (0..256)], index 0xFF = "the run holds
+//     this cell".  A consumer fetches the 8 entries of its run with two LDS.128 per angle (what counts on the LDS
+//     pipe is the 128 B/clk returned to the register file, so a broadcast 16-byte entry per voxel would cost as much
+//     as a cell: the first version of this kernel did that and ran at 4.46 ms instead of bp_kernel's 5.57).
 //   * "Parity registers": consecutive voxels of a run move the detector coordinate by |sc| <= 1 cell, so of the
 //     two cells (c, c+1) of a sample one is even and one is odd and each is usually the cell held from the previous
 //     voxel: a run loads 2 + 7|cos| cells instead of 16 (2.5x fewer LDS wavefronts on average).
-//   * setmaxnreg: the helper warpgroup drops to 40 registers, the four consumer warpgroups grow to 104 (640 x 96 launch registers = 512 x 104 + 128 x 40 + slack: setmaxnreg.inc can only take what .dec released).
+//   * setmaxnreg: the helper warpgroup drops to 40 registers, the four consumer warpgroups grow to 104 (640 x 96
+//     launch registers = 512 x 104 + 128 x 40 + slack: setmaxnreg.inc can only take what .dec released).
 #pragma once
 #include "ttv_bp.cuh"
 
@@ -31,24 +36,33 @@ constexpr int BPT_NW = 16;                      // consumer warps = runs per til
 constexpr int BPT_TX = 16, BPT_TY = 8;          // tile: two runs along X, eight rows
 constexpr int BPT_CW = 21;                      // detector cells per angle window: 15|sc| + 7|ss| <= 16.6 -> cells 1..19 used, one spare at either end
 constexpr int BPT_NS = 8;                       // angle slots in flight
-constexpr uint32_t BPT_XBS = BPT_CW * 128u;     // x-block stride inside a slot
-constexpr uint32_t BPT_DATA = BPT_XB * BPT_XBS;
-constexpr uint32_t BPT_TAB = BPT_NW * BPT_VT * 16u;
+constexpr uint32_t BPT_CELL = BPT_XB * 128u;    // bytes of one staged cell (8 x-blocks)
+constexpr uint32_t BPT_DATA = BPT_CW * BPT_CELL;
+constexpr uint32_t BPT_TAB = BPT_NW * BPT_VT * 4u;
 constexpr uint32_t BPT_SLOT = BPT_DATA + BPT_TAB;
 constexpr int BPT_THREADS = (BPT_NW + 4) * 32;
 constexpr size_t BPT_SMEM = (size_t)BPT_NS * BPT_SLOT + 2 * BPT_NS * sizeof(uint64_t);
 
-// two predicated LDS.128 (x-blocks 2q and 2q+1 of one cell): loaded only when the entry's offset is not flagged
-// "held" (bit 31); the registers keep their values otherwise
-__device__ __forceinline__ void lds_cell_if(float4& a, float4& b, uint32_t entry_off, uint32_t lane_base) {
+// two predicated LDS.128 (x-blocks 2q and 2q+1 of cell `idx`, CELLB bytes per cell): loaded unless idx == 0xFF
+// ("the run holds this cell"); the registers keep their values otherwise
+template <uint32_t CELLB>
+__device__ __forceinline__ void lds_cell_if(float4& a, float4& b, uint32_t idx, uint32_t lane_base) {
     asm volatile(
         "{\n\t.reg .pred p;\n\t.reg .u32 ad;\n\t"
-        "setp.ge.s32 p, %8, 0;\n\t"
-        "add.u32 ad, %8, %9;\n\t"
+        "setp.ne.u32 p, %8, 255;\n\t"
+        "mad.lo.u32 ad, %8, %10, %9;\n\t"
         "@p ld.shared.v4.f32 {%0,%1,%2,%3}, [ad];\n\t"
-        "@p ld.shared.v4.f32 {%4,%5,%6,%7}, [ad+%10];\n\t}"
+        "@p ld.shared.v4.f32 {%4,%5,%6,%7}, [ad+128];\n\t}"
         : "+f"(a.x), "+f"(a.y), "+f"(a.z), "+f"(a.w), "+f"(b.x), "+f"(b.y), "+f"(b.z), "+f"(b.w)
-        : "r"(entry_off), "r"(lane_base), "n"(BPT_XBS));
+        : "r"(idx), "r"(lane_base), "n"(CELLB));
+}
+// 32-bit table entry [even-cell index : 8 | odd-cell index : 8 | 256 * weight of the even cell : 16]
+__device__ __forceinline__ uint32_t entry_iE(uint32_t e) { return e & 0xFFu; }
+__device__ __forceinline__ uint32_t entry_iO(uint32_t e) { return __byte_perm(e, 0u, 0x4441u); }
+__device__ __forceinline__ float entry_wE(uint32_t e) {          // bytes 2,3 of e under the exponent of 2^23, minus 2^23
+    uint32_t r;
+    asm("prmt.b32 %0, %1, %2, 0x7632;" : "=r"(r) : "r"(e), "r"(0x4B000000u));
+    return __uint_as_float(r) - 8388608.0f;
 }
 __device__ __forceinline__ uint4 lds128u(uint32_t addr) {
     uint4 v;
@@ -57,6 +71,9 @@ __device__ __forceinline__ uint4 lds128u(uint32_t addr) {
 }
 __device__ __forceinline__ void sts128u(uint32_t addr, uint4 v) {
     asm volatile("st.shared.v4.u32 [%0], {%1,%2,%3,%4};" ::"r"(addr), "r"(v.x), "r"(v.y), "r"(v.z), "r"(v.w) : "memory");
+}
+__device__ __forceinline__ void sts32u(uint32_t addr, uint32_t v) {
+    asm volatile("st.shared.u32 [%0], %1;" ::"r"(addr), "r"(v) : "memory");
 }
 
 template <int EPI>
@@ -93,10 +110,8 @@ bpt_kernel(const __grid_constant__ CUtensorMap tmS, const BpParams p, int nxb)
             const float ay0 = -fY0 * k.y, ay1 = -(fY0 + (float)(BPT_TY - 1)) * k.y;
             const float fmin = fminf(ax0, ax1) + fminf(ay0, ay1) + k.z;
             const int w0 = (int)floorf(fmin - 0.5f) - 1;
-            if (lane == 0) tma_load_4d(smem_raw + (size_t)s * BPT_SLOT, &tmS, &full[s], 0, w0, a, xb0);
+            if (lane == 0) tma_load_4d(smem_raw + (size_t)s * BPT_SLOT, &tmS, &full[s], 0, xb0, w0, a);
             const float Cl = TTV_MAGIC_C(w0);
-            const float ws = k.w * (1.0f / 512.0f);
-            const float w256 = 512.0f * ws;
 #pragma unroll
             for (int i = 0; i < BPT_NW * BPT_VT / 32; ++i) {
                 const int v = i * 32 + lane, run = v >> 3, t = v & 7;
@@ -108,21 +123,15 @@ bpt_kernel(const __grid_constant__ CUtensorMap tmS, const BpParams p, int nxb)
                 const uint32_t u = (uint32_t)(__float_as_int(tt) - TTV_MAGIC_BITS);
                 int ci = (int)(u >> 9);
                 ci = min(max(ci, 0), BPT_CW - 2);                       // never leaves the window (margin in BPT_CW); keeps a bad geometry from faulting
-                const float al = __int_as_float((int)((u & 0x1FEu) | 0x4B000000u)) - 8388608.0f;
-                const float w1 = al * ws;
-                const float wl = fmaf(-al, ws, w256);
+                const uint32_t a8 = (u >> 1) & 0xFFu;                   // 256 * weight of the upper cell
                 const int cE = (ci + 1) & ~1, cO = ci | 1;
                 const int cip = __shfl_up_sync(0xffffffffu, ci, 1);
                 const bool first = (t == 0);
                 const bool keepE = !first && (((cip + 1) & ~1) == cE);
                 const bool keepO = !first && ((cip | 1) == cO);
-                const bool odd = (ci & 1) != 0;
-                uint4 e;
-                e.x = (uint32_t)cE * 128u | (keepE ? 0x80000000u : 0u);
-                e.y = (uint32_t)cO * 128u | (keepO ? 0x80000000u : 0u);
-                e.z = __float_as_uint(odd ? w1 : wl);
-                e.w = __float_as_uint(odd ? wl : w1);
-                sts128u(s_base + (uint32_t)s * BPT_SLOT + BPT_DATA + (uint32_t)v * 16u, e);
+                const uint32_t wE = (ci & 1) ? a8 : 256u - a8;
+                sts32u(s_base + (uint32_t)s * BPT_SLOT + BPT_DATA + (uint32_t)v * 4u,
+                       (keepE ? 0xFFu : (uint32_t)cE) | ((keepO ? 0xFFu : (uint32_t)cO) << 8) | (wE << 16));
             }
             __syncwarp();
             if (lane == 0) mbar_arrive_expect_tx(&full[s], BPT_DATA);
@@ -135,7 +144,7 @@ bpt_kernel(const __grid_constant__ CUtensorMap tmS, const BpParams p, int nxb)
     const int Y = y0 + (warp >> 1);
     const int Xb = x0 + (warp & 1) * BPT_VT;
     const int xbA = xb0 + (lane >> 3) * 2;
-    const uint32_t lane_off = (uint32_t)(lane >> 3) * 2u * BPT_XBS + (uint32_t)(lane & 7) * 16u;
+    const uint32_t lane_off = (uint32_t)(lane >> 3) * 256u + (uint32_t)(lane & 7) * 16u;
 
     Acc4 acc1[BPT_VT], acc2[BPT_VT];
 #pragma unroll
@@ -148,14 +157,19 @@ bpt_kernel(const __grid_constant__ CUtensorMap tmS, const BpParams p, int nxb)
         const int s = a % BPT_NS;
         mbar_wait(&full[s], (a / BPT_NS) & 1);
         const uint32_t slot = s_base + (uint32_t)s * BPT_SLOT;
-        const uint32_t tab = slot + BPT_DATA + (uint32_t)warp * (BPT_VT * 16u);
+        const uint32_t tab = slot + BPT_DATA + (uint32_t)warp * (BPT_VT * 4u);
         const uint32_t lb = slot + lane_off;
+        const uint4 ea = lds128u(tab), eb = lds128u(tab + 16u);
+        const uint32_t ent[BPT_VT] = {ea.x, ea.y, ea.z, ea.w, eb.x, eb.y, eb.z, eb.w};
+        const float sc256 = c_bp_angle[a].w;                 // per-angle scale (par_bp.cu:178); weights are in 1/256
+        const float ws = sc256 * (1.0f / 256.0f);
 #pragma unroll
         for (int t = 0; t < BPT_VT; ++t) {
-            const uint4 e = lds128u(tab + (uint32_t)t * 16u);
-            lds_cell_if(E1, E2, e.x, lb);
-            lds_cell_if(O1, O2, e.y, lb);
-            const float wE = __uint_as_float(e.z), wO = __uint_as_float(e.w);
+            const uint32_t e = ent[t];
+            lds_cell_if<BPT_CELL>(E1, E2, entry_iE(e), lb);
+            lds_cell_if<BPT_CELL>(O1, O2, entry_iO(e), lb);
+            const float w8 = entry_wE(e);
+            const float wE = w8 * ws, wO = fmaf(-w8, ws, sc256);
             acc1[t].fma(wE, E1); acc1[t].fma(wO, O1);
             acc2[t].fma(wE, E2); acc2[t].fma(wO, O2);
         }

@@ -600,7 +600,7 @@ public:
         p.N = N; p.Nd = N; p.Na = Na; p.vol = vol; p.C = C.p; p.step = step;
         // table-driven kernel (ttv_bpt.cuh): 8 x-blocks per CTA; the classic kernel serves thin slabs
         if (bp_variant == 2 || (bp_variant == 0 && zb >= 5)) {
-            CUtensorMap tmT = make_tmap(sino, N, Na, zb, BPT_CW, 1, 32, BPT_XB);
+            CUtensorMap tmT = make_tmap_xb(sino, N, Na, zb, BPT_XB, BPT_CW, 1);
             dim3 gridT((N + BPT_TX - 1) / BPT_TX, (N + BPT_TY - 1) / BPT_TY, (zb + BPT_XB - 1) / BPT_XB);
             ProfScope ps(*this, PF_BP);
             bpt_kernel<EPI><<<gridT, BPT_THREADS, BPT_SMEM, st>>>(tmT, p, zb);

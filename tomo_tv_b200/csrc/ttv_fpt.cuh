@@ -41,17 +41,7 @@ static_assert(FPT_NH * 32 == FPT_RUNS * 2, "one helper thread per half run");
 
 __host__ __device__ inline uint32_t fpt_slot_bytes(int CW) { return (uint32_t)CW * (FPT_XB * 128u) + FPT_TAB; }
 
-// cell `idx` (x-blocks 0 and 1) into a/b unless idx == 0xFF ("held")
-__device__ __forceinline__ void lds_cell2_if(float4& a, float4& b, uint32_t idx, uint32_t lane_base) {
-    asm volatile(
-        "{\n\t.reg .pred p;\n\t.reg .u32 ad;\n\t"
-        "setp.ne.u32 p, %8, 255;\n\t"
-        "mad.lo.u32 ad, %8, 256, %9;\n\t"
-        "@p ld.shared.v4.f32 {%0,%1,%2,%3}, [ad];\n\t"
-        "@p ld.shared.v4.f32 {%4,%5,%6,%7}, [ad+128];\n\t}"
-        : "+f"(a.x), "+f"(a.y), "+f"(a.z), "+f"(a.w), "+f"(b.x), "+f"(b.y), "+f"(b.z), "+f"(b.w)
-        : "r"(idx), "r"(lane_base));
-}
+constexpr uint32_t FPT_CELL = FPT_XB * 128u;    // bytes of one staged cell (2 x-blocks)
 
 template <int EPI>
 __global__ void __launch_bounds__(FPT_THREADS, 1)
@@ -166,7 +156,6 @@ fpt_kernel(const __grid_constant__ CUtensorMap tmV, const __grid_constant__ CUte
     for (int t = 0; t < FP_RT; ++t) { acc1[t].zero(); acc2[t].zero(); }
     float4 E1 = make_float4(0.f, 0.f, 0.f, 0.f), E2 = E1, O1 = E1, O2 = E1;
     const uint32_t tab_off = data_bytes + (uint32_t)run * (FP_RT * 4u);
-    const uint32_t magic = 0x4B000000u;
 
 #pragma unroll 1
     for (int line = 0; line < N; ++line) {
@@ -180,9 +169,9 @@ fpt_kernel(const __grid_constant__ CUtensorMap tmV, const __grid_constant__ CUte
 #pragma unroll
             for (int t = 0; t < FP_RT; ++t) {
                 const uint32_t e = ent[t];
-                lds_cell2_if(E1, E2, e & 0xFFu, lb);
-                lds_cell2_if(O1, O2, __byte_perm(e, 0u, 0x4441u), lb);
-                const float wE = __uint_as_float(__byte_perm(e, magic, 0x7632u)) - 8388608.0f;
+                lds_cell_if<FPT_CELL>(E1, E2, entry_iE(e), lb);
+                lds_cell_if<FPT_CELL>(O1, O2, entry_iO(e), lb);
+                const float wE = entry_wE(e);
                 const float wO = 256.0f - wE;
                 acc1[t].fma(wE, E1); acc1[t].fma(wO, O1);
                 acc2[t].fma(wE, E2); acc2[t].fma(wO, O2);
