@@ -181,9 +181,9 @@ def test_lane_mappings_of_the_table_driven_projectors_cover_their_tiles_once():
     assert [h * 16 for h in range(128)] == [run * 32 + half * 16 for run in range(64) for half in range(2)]
 
 
-@pytest.mark.parametrize("tx,ty,cw", [(16, 16, 26), (16, 8, 21)])
+@pytest.mark.parametrize("tx,ty,cw", [(16, 16, 27), (16, 8, 22)])
 def test_bp_detector_windows_hold_every_sample_of_the_tile(tx, ty, cw):
-    """Window sizing of bp_kernel (16 x 16 tile, BP_CW = 26) and bpt_kernel (16 x 8, BPT_CW = 21),
+    """Window sizing of bp_kernel (16 x 16 tile, BP_CW = 27) and bpt_kernel (16 x 8, BPT_CW = 22),
     restated from the producer code: w0 = floor(fmin - 0.5) - 1 with fmin the smallest detector coordinate of the
     tile's corners; every voxel's cell pair (c, c+1) relative to w0 must lie inside [0, cw)."""
     rng = np.random.default_rng(tx)
@@ -198,7 +198,7 @@ def test_bp_detector_windows_hold_every_sample_of_the_tile(tx, ty, cw):
             ax0, ax1 = fx0 * c, np.float32(fx0 + np.float32(tx - 1)) * c
             ay0, ay1 = -fy0 * s, -np.float32(fy0 + np.float32(ty - 1)) * s
             fmin = np.float32(np.float32(min(ax0, ax1) + min(ay0, ay1)) + off)
-            w0 = int(np.floor(np.float32(fmin - np.float32(0.5)))) - 1
+            w0 = (int(np.floor(np.float32(fmin - np.float32(0.5)))) - 1) & ~1      # even start
             fx = (np.arange(x0, x0 + tx) - 0.5 * n + 0.5)[None, :]
             fy = (np.arange(y0, y0 + ty) - 0.5 * n + 0.5)[:, None]
             cell = np.floor(fx * float(c) - fy * float(s) + float(off) - 0.5).astype(int) - w0

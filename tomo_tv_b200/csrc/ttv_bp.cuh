@@ -21,7 +21,7 @@ constexpr int BP_TILE = 16;
 constexpr int BP_VT = 8;       // voxels per lane
 constexpr int BP_NW = 8;       // consumer warps
 constexpr int BP_TA = 16;      // angles per stage
-constexpr int BP_CW = 26;      // detector cells per angle window
+constexpr int BP_CW = 27;      // detector cells per angle window (26 + 1: the window starts at an even cell)
 constexpr int BP_S = 2;        // stages
 constexpr int BP_THREADS = (BP_NW + 1) * 32;
 constexpr int BP_MAX_ANGLES = 2048;
@@ -113,7 +113,9 @@ bp_kernel(const __grid_constant__ CUtensorMap tmS, const BpParams p)
                 const float ax0 = fX0 * k.x, ax1 = (fX0 + (float)(BP_TILE - 1)) * k.x;
                 const float ay0 = -fY0 * k.y, ay1 = -(fY0 + (float)(BP_TILE - 1)) * k.y;
                 const float fmin = fminf(ax0, ax1) + fminf(ay0, ay1) + k.z;
-                const int w0 = (int)floorf(fmin - 0.5f) - 1;
+                // even start: the parity of a window-relative cell index is the parity of the detector cell, so
+                // "even cell first" means the same in bp_kernel and bpt_kernel whatever their tiles
+                const int w0 = ((int)floorf(fmin - 0.5f) - 1) & ~1;
                 s_C[s * BP_TA + lane] = TTV_MAGIC_C(w0);
                 tma_load_4d(smem_raw + (size_t)s * BP_STAGE_BYTES + (size_t)lane * BP_ANGLE_BYTES, &tmS, &full[s], 0, w0, a, xb);
             }
@@ -161,10 +163,13 @@ bp_kernel(const __grid_constant__ CUtensorMap tmS, const BpParams p)
                 const float al = __int_as_float((int)((u & 0x1FEu) | 0x4B000000u)) - 8388608.0f;
                 const float w1 = al * ws;
                 const float w0 = fmaf(-al, ws, w256);
-                const float4 v0 = lds128(base + off);
-                const float4 v1 = lds128(base + off + 128u);
-                acc[t].fma(w0, v0);      // acc = fmaf(w1, v1, fmaf(w0, v0, acc)), 4 FFMA2
-                acc[t].fma(w1, v1);
+                // even cell first, whichever of the pair it is: the accumulation order of the table-driven kernel
+                // (ttv_bpt.cuh), so that thin and thick slabs -- 1 or 8 GPUs -- give bit-identical volumes
+                const bool odd = (off & 128u) != 0u;
+                const float4 vE = lds128(base + ((off + 128u) & ~128u));
+                const float4 vO = lds128(base + (off | 128u));
+                acc[t].fma(odd ? w1 : w0, vE);      // acc = fmaf(wO, vO, fmaf(wE, vE, acc)), 4 FFMA2
+                acc[t].fma(odd ? w0 : w1, vO);
             }
         }
         __syncwarp();

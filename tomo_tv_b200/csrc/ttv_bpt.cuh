@@ -2,9 +2,9 @@
 // registers.  sm_100a.  Default back projector for slabs of >= 5 x-blocks (ttv_engine.cuh: Engine::bp).
 //
 // Arithmetic: the reference's devBP (A/cuda/2d/par_bp.cu:52-87), sample position, 8-bit texture weights and
-// per-angle scale as in bp_kernel (ttv_bp.cuh); the two taps of a sample are accumulated even-cell-first
-// (bp_kernel: lower-cell-first) and the weight of the even cell is one rounded product, i.e. the result differs
-// from bp_kernel's by rounding (~1e-7), not systematically.
+// per-angle scale as in bp_kernel (ttv_bp.cuh); both kernels accumulate the two taps of a sample even-cell-first
+// over ascending angles and their weights are the same single roundings of the same real numbers (256*ws' == scale
+// exactly), so bpt_kernel and bp_kernel are bit-identical (tests/test_gpu_table_kernels.py).
 //
 // Why (profiles/r2b_*): bp_kernel spends 8 B of shared-memory reads and ~5.5 instructions per sample; ncu shows
 // its LDS pipe 95 % busy.  Register-reuse variants with per-lane index arithmetic halved the LDS wavefronts but
@@ -34,7 +34,7 @@ constexpr int BPT_XB = 8;                       // x-blocks per CTA
 constexpr int BPT_VT = 8;                       // voxels per run
 constexpr int BPT_NW = 16;                      // consumer warps = runs per tile
 constexpr int BPT_TX = 16, BPT_TY = 8;          // tile: two runs along X, eight rows
-constexpr int BPT_CW = 21;                      // detector cells per angle window: 15|sc| + 7|ss| <= 16.6 -> cells 1..19 used, one spare at either end
+constexpr int BPT_CW = 22;                      // detector cells per angle window: 15|sc| + 7|ss| <= 16.6 -> 19 cells, one spare at either end, + 1 for the even start
 constexpr int BPT_NS = 8;                       // angle slots in flight
 constexpr uint32_t BPT_CELL = BPT_XB * 128u;    // bytes of one staged cell (8 x-blocks)
 constexpr uint32_t BPT_DATA = BPT_CW * BPT_CELL;
@@ -109,7 +109,7 @@ bpt_kernel(const __grid_constant__ CUtensorMap tmS, const BpParams p, int nxb)
             const float ax0 = fX0 * k.x, ax1 = (fX0 + (float)(BPT_TX - 1)) * k.x;
             const float ay0 = -fY0 * k.y, ay1 = -(fY0 + (float)(BPT_TY - 1)) * k.y;
             const float fmin = fminf(ax0, ax1) + fminf(ay0, ay1) + k.z;
-            const int w0 = (int)floorf(fmin - 0.5f) - 1;
+            const int w0 = ((int)floorf(fmin - 0.5f) - 1) & ~1;          // even start: window-relative parity = detector-cell parity (as bp_kernel)
             if (lane == 0) tma_load_4d(smem_raw + (size_t)s * BPT_SLOT, &tmS, &full[s], 0, xb0, w0, a);
             const float Cl = TTV_MAGIC_C(w0);
 #pragma unroll

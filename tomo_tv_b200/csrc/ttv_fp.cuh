@@ -196,10 +196,13 @@ fp_kernel(const __grid_constant__ CUtensorMap tmV, const __grid_constant__ CUten
                 const uint32_t off = (u >> 9) << 7;
                 const float w1 = __int_as_float((int)((u & 0x1FEu) | 0x4B000000u)) - 8388608.0f;   // 512*alpha
                 const float w0 = 512.0f - w1;
-                const float4 v0 = lds128(base + off);
-                const float4 v1 = lds128(base + off + 128u);
-                acc[t].fma(w0, v0);      // acc = fmaf(w1, v1, fmaf(w0, v0, acc)), 4 FFMA2
-                acc[t].fma(w1, v1);
+                // even cell first, whichever of the pair it is: the accumulation order of the table-driven kernel
+                // (ttv_fpt.cuh), so that thin and thick slabs -- 1 or 8 GPUs -- give bit-identical sinograms
+                const bool odd = (off & 128u) != 0u;
+                const float4 vE = lds128(base + ((off + 128u) & ~128u));
+                const float4 vO = lds128(base + (off | 128u));
+                acc[t].fma(odd ? w1 : w0, vE);      // acc = fmaf(wO, vO, fmaf(wE, vE, acc)), 4 FFMA2
+                acc[t].fma(odd ? w0 : w1, vO);
             }
         }
         __syncwarp();

@@ -4,9 +4,9 @@
 //
 // Arithmetic: the reference's FPvertical_simple / FPhorizontal_simple (A/cuda/2d/par_fp.cu:53-200): sample
 // positions by the same float32 operations as fp_kernel (ttv_fp.cuh; restart every 64 lines, par_fp.cu:49,282-286),
-// 8-bit texture weights (A/cuda/2d/util.cu:161-179).  The two taps of a sample are accumulated even-cell-first
-// and with weights in 1/256 instead of 1/512 (both exact), so a result differs from fp_kernel's by at most one
-// rounding per sample.
+// 8-bit texture weights (A/cuda/2d/util.cu:161-179).  Both kernels accumulate the two taps of a sample
+// even-cell-first over ascending lines; weights here are in 1/256 instead of 1/512 (an exact power-of-two scaling
+// of every intermediate), so fpt_kernel and fp_kernel are bit-identical (tests/test_gpu_table_kernels.py).
 //
 // Why (profiles/r2b_*): fp_kernel reads 8 B of shared memory per sample (LDS pipe 90 % busy); neighbouring
 // detectors of a ray run are 1 .. 1.41 cells apart, so the upper cell of detector t is usually the lower cell of
