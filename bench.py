@@ -25,9 +25,16 @@ import numpy as np
 ROOT = os.path.dirname(os.path.abspath(__file__))
 sys.path.insert(0, ROOT)
 
-# dram__bytes_read.sum + dram__bytes_write.sum per launch, ncu --set full at 512^3 x 180 on 1 B200 (profiles/r1h_dram_raw.csv)
-TRAFFIC_512 = {"fgp_sweep": 3803738000, "fgp_first": 2109190000, "fgp_final": 2734996000, "momentum": 2624425000, "tv": 576208000,
-               "fp": 984207000, "bp": 1217342000}
+def traffic_512():
+    """dram__bytes_read.sum + dram__bytes_write.sum per launch from the committed `ncu --set full` capture of this round's
+    default kernels at 512^3 x 180 on one B200 (profiles/traffic_512.json, written by scripts/ncu_traffic.py from the
+    .ncu-rep); no capture -> no number (traffic: null)."""
+    try:
+        return json.load(open(os.path.join(ROOT, "profiles", "traffic_512.json")))
+    except Exception:
+        return {}
+
+
 METRIC = "fista_tv_iters_per_sec"
 UNIT = "iterations/s"
 LAMBDA, NTV = 0.1, 10
@@ -144,7 +151,10 @@ def run_reference(args):
     if rank != 0:
         return
     cores = os.cpu_count() or 1
-    nslab = max(1, min(cores, args.size))
+    # torchrun exports OMP_NUM_THREADS=1 to its workers: this arm is the CPU baseline "with all the host threads it can
+    # use", so the thread count is set explicitly before the OpenMP runtime of oracle/liboracle.so starts
+    os.environ["OMP_NUM_THREADS"] = str(cores)
+    nslab = min(args.size, max(64, cores))               # >= 64 slices per step: a bounded SAMPLE of the job, scaled below
     sec, threads = cpu_fista_sample(args.size, args.angles, nslab, args.steps, args.warmup)
     value = (1.0 / sec) * (nslab / args.size)          # iterations/s of the FULL job at this per-slice rate
     line = {
@@ -152,6 +162,7 @@ def run_reference(args):
         "warmup": args.warmup, "ms_per_step": sec * 1e3 * (args.size / nslab), "higher_is_better": True, "scaling": "strong",
         "vs_baseline": None, "dtype": "f32", "data": "synthetic",
         "config": {"workload": f"FISTA-TV {args.size}^3 x {args.angles} angles, nTViter={NTV}, lambda={LAMBDA}",
+                   "sampled": f"{nslab} of {args.size} slices timed per step; value = per-slice rate x {args.size}/{nslab} (slices are independent on the CPU path)",
                    "note": "reference GPU path needs CUDA; its CPU package (tomofusion/cpu) has no TV-FGP/FISTA, so the CPU arm is the "
                            "oracle restatement of the same iteration (oracle/oracle.c, OpenMP over slices)"},
         "cpu_baseline": {"value": value, "unit": UNIT, "cores": threads, "kind": "port",
@@ -272,6 +283,17 @@ def run_ours(args):
     e2e_s = allmax(time.perf_counter() - t0)
     barrier()
     e2e_value = args.steps / e2e_s
+    # the reconstruction the end-to-end leg produced, as one hash that does not depend on how many GPUs it was sharded
+    # over: sha256 over the per-slice sha256 digests in global slice order (every kernel on the path computes a voxel
+    # with the same operations whatever the slab thickness, so the hashes of the 1-, 2-, 4- and 8-GPU runs are equal)
+    import hashlib
+    digests = [hashlib.sha256(out_np[i].tobytes()).digest() for i in range(nloc)]
+    if dist is not None:
+        allg = [None] * world
+        dist.all_gather_object(allg, (x0, digests))
+        digests = [d for _, ds in sorted(allg, key=lambda t: t[0]) for d in ds]
+    recon_sha = hashlib.sha256(b"".join(digests)).hexdigest()
+    recon_tv = eng.tv()                                         # TV of the final volume (all-reduced scalar)
 
     # ---------------- roofline of the dominant kernel ----------------
     pk, pk_kind = peaks()
@@ -301,22 +323,26 @@ def run_ours(args):
     if dom:
         roof = {"kernel": {"fgp_sweep": "fgp_tile_kernel<SWEEP>", "fgp_first": "fgp_tile_kernel<FIRST>", "fgp_final": "fgp_tile_kernel<FINAL>"}.get(dom, dom),
                 "bound": "hbm", "achieved": groups[dom]["achieved_gbs"], "peak": pk["hbm_gbs"], "unit": "GB/s",
-                "frac": groups[dom]["frac_of_hbm_peak"], "traffic": TRAFFIC_512.get(dom) if (n, na, world) == (512, 180, 1) else None, "peak_kind": pk_kind,
+                "frac": groups[dom]["frac_of_hbm_peak"], "traffic": traffic_512().get(dom) if (n, na, world) == (512, 180, 1) else None, "peak_kind": pk_kind,
                 "algorithmic_bytes_per_launch": alg_bytes[dom], "share_of_step": groups[dom]["share_of_step"],
-                "traffic_note": "dram__bytes_read.sum + dram__bytes_write.sum per launch, ncu --set full at 512^3 x 180 on 1 GPU (profiles/r1h_dram_raw.csv)"}
+                "traffic_note": "dram__bytes_read.sum + dram__bytes_write.sum per launch from profiles/traffic_512.json (ncu --set full, 512^3 x 180, 1 GPU); null without a capture"}
     sm_mhz = (clk or {}).get("sm_mhz") or pk.get("sm_max_mhz") or 1965.0
     try:
         n_sm = torch.cuda.get_device_properties(local).multi_processor_count
     except Exception:
         n_sm = 148
     lds_peak = n_sm * 128 * sm_mhz * 1e6 / 1e9
+    # shared-memory bytes per bilinear sample of the default kernels: register-file deliveries (LDS wavefronts
+    # x 128 B) + TMA fill, measured with ncu (profiles/r2d_*): fpt_kernel 1345 + 316 wavefronts per 32768 samples,
+    # bpt_kernel 897 + 168 per 32768; the classic kernels (thin slabs) read 8 B per sample + fill
+    lds_model = {"fp": (1345 + 316) * 128 / 32768.0 if nloc >= 128 else 8.0 + 1.25, "bp": (897 + 168) * 128 / 32768.0 if nloc >= 64 else 8.0 + 0.4}
     proj_roof = {}
     for g in ("fp", "bp"):
         if g in groups:
-            ach = samples * 8 / (groups[g]["ms_per_launch"] * 1e-3) / 1e9
+            ach = samples * lds_model[g] / (groups[g]["ms_per_launch"] * 1e-3) / 1e9
             proj_roof[g] = {"bound": "shared-memory", "achieved": ach, "peak": lds_peak, "unit": "GB/s", "frac": ach / lds_peak,
                             "samples_per_s": groups[g]["samples_per_s"], "share_of_step": groups[g]["share_of_step"],
-                            "lds_bytes_per_sample": 8, "peak_def": f"{n_sm} SMs x 128 B/clk x {sm_mhz:.0f} MHz"}
+                            "smem_bytes_per_sample": lds_model[g], "peak_def": f"{n_sm} SMs x 128 B/clk x {sm_mhz:.0f} MHz"}
     iter_bytes = world * (74 * V + 3 * S)
     iter_roof = {"algorithmic_bytes_per_iteration": iter_bytes, "achieved_gbs": iter_bytes / (ms_per_step * 1e-3) / 1e9,
                  "frac_of_hbm_peak_x_gpus": iter_bytes / (ms_per_step * 1e-3) / 1e9 / (pk["hbm_gbs"] * world)}
@@ -333,6 +359,7 @@ def run_ours(args):
             "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": int(S / args.steps),
                     "d2h_bytes_per_step": int(V / args.steps) + 4},
             "gpu_launches": launches,
+            "recon_sha256": recon_sha, "recon_tv": recon_tv,
             "clocks": clk,
             "roofline": roof,
             "projector_roofline": proj_roof,
@@ -341,7 +368,7 @@ def run_ours(args):
         }
     if rank == 0 and world == 1 and not args.no_cpu:
         cores = os.cpu_count() or 1
-        nslab = max(1, min(cores, n))
+        nslab = min(n, max(64, cores))
         sec, threads = cpu_fista_sample(n, na, nslab, 2, 1)
         line["cpu_baseline"] = {"value": (1.0 / sec) * (nslab / n), "unit": UNIT, "cores": threads, "kind": "port",
                                 "sample": f"{nslab} of {n} slices per step (2 timed iterations), scaled by {n}/{nslab}"}

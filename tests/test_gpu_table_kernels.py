@@ -26,9 +26,9 @@ def test_bpt_matches_bp(ttv, nx, n, na):
     sino = rng.standard_normal((nx, na * n)).astype(np.float32)
     b = rng.random((nx, na * n), dtype=np.float32) * 3
     outs = []
-    for v in (1, 2):
+    for v, xb in ((1, 0), (2, 2), (2, 8)):
         eng = ttv.tomoengine(nx, n, ang)
-        eng.set_option("bp_variant", v); eng.set_option("fp_variant", 1)
+        eng.set_option("bp_variant", v); eng.set_option("bp_xb", xb); eng.set_option("fp_variant", 1)
         eng.initialize_initial_volume()
         eng.set_model_projections(sino); eng.back_projection()
         bp = eng.get_recon_all()
@@ -38,9 +38,10 @@ def test_bpt_matches_bp(ttv, nx, n, na):
         eng.set_recon_all(np.full((nx, n, n), 0.3, np.float32))
         cost = [eng.poisson_ML(0.4) for _ in range(2)]
         outs.append((bp, sirt, eng.get_recon_all(), cost))
-    for a, c in zip(outs[0][:3], outs[1][:3]):
-        assert np.array_equal(a, c)
-    assert np.allclose(outs[0][3], outs[1][3], rtol=1e-5)
+    for other in outs[1:]:
+        for a, c in zip(outs[0][:3], other[:3]):
+            assert np.array_equal(a, c)
+        assert np.allclose(outs[0][3], other[3], rtol=1e-5)
 
 
 @pytest.mark.parametrize("nx,n,na", SIZES)
@@ -70,7 +71,7 @@ def test_fpt_matches_fp(ttv, nx, n, na):
 
 
 def test_default_choice_by_slab_thickness(ttv):
-    """Default = table-driven kernels where they fill their CTAs (FP: >= 2 x-blocks, BP: >= 5), classic otherwise;
+    """Default = table-driven kernels from 2 x-blocks on (BP: 2 x-blocks per CTA below 7 x-blocks, 8 above), classic for one;
     both give the same reconstruction bit for bit."""
     rng = np.random.default_rng(3)
     nx, n, na = 200, 64, 20

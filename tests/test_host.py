@@ -181,9 +181,9 @@ def test_lane_mappings_of_the_table_driven_projectors_cover_their_tiles_once():
     assert [h * 16 for h in range(128)] == [run * 32 + half * 16 for run in range(64) for half in range(2)]
 
 
-@pytest.mark.parametrize("tx,ty,cw", [(16, 16, 27), (16, 8, 22)])
+@pytest.mark.parametrize("tx,ty,cw", [(16, 16, 27), (16, 8, 22), (32, 16, 40)])
 def test_bp_detector_windows_hold_every_sample_of_the_tile(tx, ty, cw):
-    """Window sizing of bp_kernel (16 x 16 tile, BP_CW = 27) and bpt_kernel (16 x 8, BPT_CW = 22),
+    """Window sizing of bp_kernel (16 x 16 tile, BP_CW = 27) and bpt_kernel (16 x 8: CW = 22; 32 x 16: CW = 40),
     restated from the producer code: w0 = floor(fmin - 0.5) - 1 with fmin the smallest detector coordinate of the
     tile's corners; every voxel's cell pair (c, c+1) relative to w0 must lie inside [0, cw)."""
     rng = np.random.default_rng(tx)

@@ -30,18 +30,30 @@
 
 namespace ttv {
 
-constexpr int BPT_XB = 8;                       // x-blocks per CTA
 constexpr int BPT_VT = 8;                       // voxels per run
-constexpr int BPT_NW = 16;                      // consumer warps = runs per tile
-constexpr int BPT_TX = 16, BPT_TY = 8;          // tile: two runs along X, eight rows
-constexpr int BPT_CW = 22;                      // detector cells per angle window: 15|sc| + 7|ss| <= 16.6 -> 19 cells, one spare at either end, + 1 for the even start
+constexpr int BPT_NW = 16;                      // consumer warps
 constexpr int BPT_NS = 8;                       // angle slots in flight
-constexpr uint32_t BPT_CELL = BPT_XB * 128u;    // bytes of one staged cell (8 x-blocks)
-constexpr uint32_t BPT_DATA = BPT_CW * BPT_CELL;
-constexpr uint32_t BPT_TAB = BPT_NW * BPT_VT * 4u;
-constexpr uint32_t BPT_SLOT = BPT_DATA + BPT_TAB;
 constexpr int BPT_THREADS = (BPT_NW + 4) * 32;
-constexpr size_t BPT_SMEM = (size_t)BPT_NS * BPT_SLOT + 2 * BPT_NS * sizeof(uint64_t);
+
+// XB = x-blocks per CTA.  8: a warp is one run (all 32 lanes = 256 slices), tile 16 x 8 voxels, one helper warp.
+//                        2: a quarter warp is one run (8 lanes = 64 slices), tile 32 x 16 voxels, four helper warps --
+//                           the same kernel for the thin slabs of a sharded volume (64 or 128 slices per GPU).
+template <int XB> struct BptCfg {
+    static constexpr int LS = 4 * XB;                               // lanes per run
+    static constexpr int RW = 32 / LS;                              // runs per warp
+    static constexpr int RUNS = BPT_NW * RW;                        // runs per tile
+    static constexpr int RX = (XB == 8) ? 2 : 4;                    // runs along X
+    static constexpr int TX = RX * BPT_VT, TY = RUNS / RX;          // tile
+    // detector cells per angle window: (TX-1)|sc| + (TY-1)|ss| <= hypot(TX-1, TY-1), + 2 cells of a sample, + one spare at
+    // either end, + 1 for the even start: 16 x 8 -> 22, 32 x 16 -> 40
+    static constexpr int CW = (XB == 8) ? 22 : 40;
+    static constexpr uint32_t CELL = XB * 128u;                     // bytes of one staged cell
+    static constexpr uint32_t DATA = CW * CELL;
+    static constexpr uint32_t TAB = RUNS * BPT_VT * 4u;
+    static constexpr uint32_t SLOT = DATA + TAB;
+    static constexpr int NH = (RUNS * BPT_VT) / 128 > 0 ? ((RUNS * BPT_VT) / 128 > 4 ? 4 : (RUNS * BPT_VT) / 128) : 1;   // helper warps (4 entries per lane)
+    static constexpr size_t SMEM = (size_t)BPT_NS * SLOT + 2 * BPT_NS * sizeof(uint64_t);
+};
 
 // two predicated LDS.128 (x-blocks 2q and 2q+1 of cell `idx`, CELLB bytes per cell): loaded unless idx == 0xFF
 // ("the run holds this cell"); the registers keep their values otherwise
@@ -76,29 +88,31 @@ __device__ __forceinline__ void sts32u(uint32_t addr, uint32_t v) {
     asm volatile("st.shared.u32 [%0], %1;" ::"r"(addr), "r"(v) : "memory");
 }
 
-template <int EPI>
+template <int EPI, int XB>
 __global__ void __launch_bounds__(BPT_THREADS, 1)
 bpt_kernel(const __grid_constant__ CUtensorMap tmS, const BpParams p, int nxb)
 {
+    using K = BptCfg<XB>;
     extern __shared__ __align__(128) unsigned char smem_raw[];
-    uint64_t* full = reinterpret_cast<uint64_t*>(smem_raw + (size_t)BPT_NS * BPT_SLOT);
+    uint64_t* full = reinterpret_cast<uint64_t*>(smem_raw + (size_t)BPT_NS * K::SLOT);
     uint64_t* empty = full + BPT_NS;
 
     const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
     const int N = p.N, Na = p.Na;
-    const int x0 = blockIdx.x * BPT_TX, y0 = blockIdx.y * BPT_TY, xb0 = blockIdx.z * BPT_XB;
+    const int x0 = blockIdx.x * K::TX, y0 = blockIdx.y * K::TY, xb0 = blockIdx.z * XB;
 
     if (tid == 0) {
-        for (int s = 0; s < BPT_NS; ++s) { mbar_init(&full[s], 1); mbar_init(&empty[s], BPT_NW); }
+        for (int s = 0; s < BPT_NS; ++s) { mbar_init(&full[s], K::NH); mbar_init(&empty[s], BPT_NW); }
         fence_barrier_init();
     }
     __syncthreads();
 
     if (warp >= BPT_NW) {
         asm volatile("setmaxnreg.dec.sync.aligned.u32 40;");
-        if (warp != BPT_NW) return;
-        // ---------------- helper warp: TMA producer + table builder ----------------
-        if (lane == 0) tma_prefetch_desc(&tmS);
+        const int hw = warp - BPT_NW;
+        if (hw >= K::NH) return;
+        // ---------------- helper warps: table builders; the first one is also the TMA producer ----------------
+        if (hw == 0 && lane == 0) tma_prefetch_desc(&tmS);
         const float fX0 = (float)x0 - 0.5f * (float)N + 0.5f;
         const float fY0 = (float)y0 - 0.5f * (float)N + 0.5f;
         const uint32_t s_base = smem_u32(smem_raw);
@@ -106,23 +120,23 @@ bpt_kernel(const __grid_constant__ CUtensorMap tmS, const BpParams p, int nxb)
             const int s = a % BPT_NS;
             if (a >= BPT_NS) mbar_wait(&empty[s], ((a / BPT_NS) - 1) & 1);
             const float4 k = c_bp_angle[a];
-            const float ax0 = fX0 * k.x, ax1 = (fX0 + (float)(BPT_TX - 1)) * k.x;
-            const float ay0 = -fY0 * k.y, ay1 = -(fY0 + (float)(BPT_TY - 1)) * k.y;
+            const float ax0 = fX0 * k.x, ax1 = (fX0 + (float)(K::TX - 1)) * k.x;
+            const float ay0 = -fY0 * k.y, ay1 = -(fY0 + (float)(K::TY - 1)) * k.y;
             const float fmin = fminf(ax0, ax1) + fminf(ay0, ay1) + k.z;
             const int w0 = ((int)floorf(fmin - 0.5f) - 1) & ~1;          // even start: window-relative parity = detector-cell parity (as bp_kernel)
-            if (lane == 0) tma_load_4d(smem_raw + (size_t)s * BPT_SLOT, &tmS, &full[s], 0, xb0, w0, a);
+            if (hw == 0 && lane == 0) tma_load_4d(smem_raw + (size_t)s * K::SLOT, &tmS, &full[s], 0, xb0, w0, a);
             const float Cl = TTV_MAGIC_C(w0);
 #pragma unroll
-            for (int i = 0; i < BPT_NW * BPT_VT / 32; ++i) {
-                const int v = i * 32 + lane, run = v >> 3, t = v & 7;
-                const float fX = (float)(x0 + (run & 1) * BPT_VT + t) - 0.5f * (float)N + 0.5f;
-                const float fY = (float)(y0 + (run >> 1)) - 0.5f * (float)N + 0.5f;
+            for (int i = 0; i < (K::RUNS * BPT_VT) / (32 * K::NH); ++i) {
+                const int v = (i * K::NH + hw) * 32 + lane, run = v >> 3, t = v & 7;
+                const float fX = (float)(x0 + (run % K::RX) * BPT_VT + t) - 0.5f * (float)N + 0.5f;
+                const float fY = (float)(y0 + (run / K::RX)) - 0.5f * (float)N + 0.5f;
                 const float myss = -__fmul_rn(fY, k.y);
                 const float fT = __fadd_rn(__fmaf_rn(fX, k.x, myss), k.z);
                 const float tt = __fmaf_rd(fT, 256.0f, Cl);
                 const uint32_t u = (uint32_t)(__float_as_int(tt) - TTV_MAGIC_BITS);
                 int ci = (int)(u >> 9);
-                ci = min(max(ci, 0), BPT_CW - 2);                       // never leaves the window (margin in BPT_CW); keeps a bad geometry from faulting
+                ci = min(max(ci, 0), K::CW - 2);                        // never leaves the window (margin in CW); keeps a bad geometry from faulting
                 const uint32_t a8 = (u >> 1) & 0xFFu;                   // 256 * weight of the upper cell
                 const int cE = (ci + 1) & ~1, cO = ci | 1;
                 const int cip = __shfl_up_sync(0xffffffffu, ci, 1);
@@ -130,21 +144,26 @@ bpt_kernel(const __grid_constant__ CUtensorMap tmS, const BpParams p, int nxb)
                 const bool keepE = !first && (((cip + 1) & ~1) == cE);
                 const bool keepO = !first && ((cip | 1) == cO);
                 const uint32_t wE = (ci & 1) ? a8 : 256u - a8;
-                sts32u(s_base + (uint32_t)s * BPT_SLOT + BPT_DATA + (uint32_t)v * 4u,
+                sts32u(s_base + (uint32_t)s * K::SLOT + K::DATA + (uint32_t)v * 4u,
                        (keepE ? 0xFFu : (uint32_t)cE) | ((keepO ? 0xFFu : (uint32_t)cO) << 8) | (wE << 16));
             }
             __syncwarp();
-            if (lane == 0) mbar_arrive_expect_tx(&full[s], BPT_DATA);
+            if (lane == 0) {
+                if (hw == 0) mbar_arrive_expect_tx(&full[s], K::DATA);
+                else mbar_arrive(&full[s]);
+            }
         }
         return;
     }
 
-    // ---------------- consumer warps: warp = run ----------------
+    // ---------------- consumer warps: run = warp (XB = 8) or quarter warp (XB = 2) ----------------
     asm volatile("setmaxnreg.inc.sync.aligned.u32 104;");
-    const int Y = y0 + (warp >> 1);
-    const int Xb = x0 + (warp & 1) * BPT_VT;
-    const int xbA = xb0 + (lane >> 3) * 2;
-    const uint32_t lane_off = (uint32_t)(lane >> 3) * 256u + (uint32_t)(lane & 7) * 16u;
+    const int lx = lane % K::LS;
+    const int run = warp * K::RW + lane / K::LS;
+    const int Y = y0 + run / K::RX;
+    const int Xb = x0 + (run % K::RX) * BPT_VT;
+    const int xbA = xb0 + (lx >> 3) * 2;
+    const uint32_t lane_off = (uint32_t)(lx >> 3) * 256u + (uint32_t)(lx & 7) * 16u;
 
     Acc4 acc1[BPT_VT], acc2[BPT_VT];
 #pragma unroll
@@ -156,8 +175,8 @@ bpt_kernel(const __grid_constant__ CUtensorMap tmS, const BpParams p, int nxb)
     for (int a = 0; a < Na; ++a) {
         const int s = a % BPT_NS;
         mbar_wait(&full[s], (a / BPT_NS) & 1);
-        const uint32_t slot = s_base + (uint32_t)s * BPT_SLOT;
-        const uint32_t tab = slot + BPT_DATA + (uint32_t)warp * (BPT_VT * 4u);
+        const uint32_t slot = s_base + (uint32_t)s * K::SLOT;
+        const uint32_t tab = slot + K::DATA + (uint32_t)run * (BPT_VT * 4u);
         const uint32_t lb = slot + lane_off;
         const uint4 ea = lds128u(tab), eb = lds128u(tab + 16u);
         const uint32_t ent[BPT_VT] = {ea.x, ea.y, ea.z, ea.w, eb.x, eb.y, eb.z, eb.w};
@@ -166,8 +185,8 @@ bpt_kernel(const __grid_constant__ CUtensorMap tmS, const BpParams p, int nxb)
 #pragma unroll
         for (int t = 0; t < BPT_VT; ++t) {
             const uint32_t e = ent[t];
-            lds_cell_if<BPT_CELL>(E1, E2, entry_iE(e), lb);
-            lds_cell_if<BPT_CELL>(O1, O2, entry_iO(e), lb);
+            lds_cell_if<K::CELL>(E1, E2, entry_iE(e), lb);
+            lds_cell_if<K::CELL>(O1, O2, entry_iO(e), lb);
             const float w8 = entry_wE(e);
             const float wE = w8 * ws, wO = fmaf(-w8, ws, sc256);
             acc1[t].fma(wE, E1); acc1[t].fma(wO, O1);
@@ -183,7 +202,7 @@ bpt_kernel(const __grid_constant__ CUtensorMap tmS, const BpParams p, int nxb)
         for (int t = 0; t < BPT_VT; ++t) {
             const int X = Xb + t;
             if (X < N) {
-                const size_t oa = (((size_t)xbA * N + Y) * N + X) * TTV_XI + (size_t)(lane & 7) * 4;
+                const size_t oa = (((size_t)xbA * N + Y) * N + X) * TTV_XI + (size_t)(lx & 7) * 4;
                 const size_t ob = oa + (size_t)N * N * TTV_XI;
                 if (xbA < nxb) *reinterpret_cast<float4*>(p.vol + oa) = bp_apply<EPI>(p, oa, acc1[t].get(), Y, X);
                 if (xbA + 1 < nxb) *reinterpret_cast<float4*>(p.vol + ob) = bp_apply<EPI>(p, ob, acc2[t].get(), Y, X);

@@ -274,6 +274,7 @@ int ttv_comm_init(ttv_handle h, const void* id128, int rank, int nranks) {
     Nccl::uid_t id; std::memcpy(&id, id128, 128);
     n.check(n.CommInitRank(&e.comm, nranks, id, rank), "ncclCommInitRank");
     e.rank = rank; e.nranks = nranks;
+    if (nranks > 1) e.prealloc_tv();
     TTV_CATCH
 }
 
@@ -332,6 +333,10 @@ int ttv_set_option(ttv_handle h, const char* name, int value) {
     else if (nm == "bp_variant") {
         if (value < 0 || value > 2) throw CudaError("ttv_set_option: bp_variant must be 0 (by slab thickness), 1 (classic) or 2 (table-driven)");
         e.bp_variant = value;
+    }
+    else if (nm == "bp_xb") {
+        if (value != 0 && value != 2 && value != 8) throw CudaError("ttv_set_option: bp_xb must be 0 (by slab thickness), 2 or 8");
+        e.bp_xb = value;
     }
     else throw CudaError("ttv_set_option: unknown option '" + nm + "'");
     TTV_CATCH

@@ -315,6 +315,17 @@ public:
         if (left64) p2p_left = open(left64);
         if (right64) p2p_right = open(right64);
         p2p_ready = true;
+        prealloc_tv();
+    }
+    // Every buffer the regularisers use, allocated when the engine joins a sharded volume (all ranks are here together,
+    // before any of them can spin on a neighbour's epoch): a cudaMalloc inside a timed / spinning call may synchronise
+    // the device or wait for a peer that is itself waiting for this rank (the round-1 deadlock at 2048^3 on 8 GPUs).
+    void prealloc_tv() {
+        use();
+        const size_t n = vol_elems();
+        if (!scratch.ok()) scratch.alloc(n);
+        for (int i = 0; i < 6; ++i) if (!P[i].ok()) P[i].alloc(n);
+        sync();
     }
 
     Engine(int nslice, int nray, const float* ang, int nang, int dev, int x_offset, int nslice_global)
@@ -542,7 +553,8 @@ public:
     }
     template <int EPI> void bp_attr() {
         TTV_CUDA(cudaFuncSetAttribute(bp_kernel<EPI>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)BP_SMEM));
-        TTV_CUDA(cudaFuncSetAttribute(bpt_kernel<EPI>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)BPT_SMEM));
+        TTV_CUDA(cudaFuncSetAttribute(bpt_kernel<EPI, 8>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)BptCfg<8>::SMEM));
+        TTV_CUDA(cudaFuncSetAttribute(bpt_kernel<EPI, 2>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)BptCfg<2>::SMEM));
     }
     void set_fp_attrs() {
         fp_attr<FP_STORE>(); fp_attr<FP_SIRT_RES>(); fp_attr<FP_KL>(); fp_attr<FP_STORE_DIST>(); fp_attr<FP_RESID>();
@@ -576,7 +588,7 @@ public:
         p.N = N; p.Nd = N; p.Na = Na; p.ndg = fp_ndg; p.CW = fp_CW; p.TR = fp_TR; p.S = fp_S;
         p.out = out; p.b = bmeas; p.R = R.p; p.red = red; p.eps = eps;
         ProfScope ps(*this, PF_FP);
-        if (fp_variant == 2 || (fp_variant == 0 && zb >= 2)) {
+        if (fp_variant == 2 || (fp_variant == 0 && zb >= 4)) {        // below 4 x-blocks the table kernel has too few CTAs for 148 SMs
             // table-driven kernel (ttv_fpt.cuh): 2 x-blocks per CTA, one line per slot
             CUtensorMap tmV = make_tmap_xb(vol, N, N, zb, FPT_XB, fp_CW, 1);
             CUtensorMap tmH = make_tmap_xb(vol, N, N, zb, FPT_XB, 1, fp_CW);
@@ -590,6 +602,12 @@ public:
         }
         TTV_LAUNCH_CHECK(); ++launches;
     }
+    template <int EPI, int XB> void bpt_launch(const float* sino, const BpParams& p, int zb) {
+        using K = BptCfg<XB>;
+        CUtensorMap tmT = make_tmap_xb(sino, N, Na, zb, XB, K::CW, 1);
+        dim3 gridT((N + K::TX - 1) / K::TX, (N + K::TY - 1) / K::TY, (zb + XB - 1) / XB);
+        bpt_kernel<EPI, XB><<<gridT, BPT_THREADS, K::SMEM, st>>>(tmT, p, zb);
+    }
     template <int EPI>
     void bp(const float* sino, float* vol, float step = 0.f, int nblocks = -1, const BpParams* extra = nullptr) {
         need_angles();
@@ -598,12 +616,10 @@ public:
         bind_bp_constants();
         BpParams p; if (extra) p = *extra;
         p.N = N; p.Nd = N; p.Na = Na; p.vol = vol; p.C = C.p; p.step = step;
-        // table-driven kernel (ttv_bpt.cuh): 8 x-blocks per CTA; the classic kernel serves thin slabs
-        if (bp_variant == 2 || (bp_variant == 0 && zb >= 5)) {
-            CUtensorMap tmT = make_tmap_xb(sino, N, Na, zb, BPT_XB, BPT_CW, 1);
-            dim3 gridT((N + BPT_TX - 1) / BPT_TX, (N + BPT_TY - 1) / BPT_TY, (zb + BPT_XB - 1) / BPT_XB);
+        // table-driven kernel (ttv_bpt.cuh): 8 x-blocks per CTA for thick slabs, 2 for thin ones; the classic kernel serves a single x-block
+        if (bp_variant == 2 || (bp_variant == 0 && zb >= 2)) {
             ProfScope ps(*this, PF_BP);
-            bpt_kernel<EPI><<<gridT, BPT_THREADS, BPT_SMEM, st>>>(tmT, p, zb);
+            if (bp_xb == 8 || (bp_xb == 0 && zb >= 7)) bpt_launch<EPI, 8>(sino, p, zb); else bpt_launch<EPI, 2>(sino, p, zb);
             TTV_LAUNCH_CHECK(); ++launches;
             return;
         }
@@ -616,6 +632,7 @@ public:
     // projector kernel choice (ttv_set_option): 0 = by slab thickness (default), 1 = classic kernel (fp_kernel / bp_kernel),
     // 2 = table-driven kernel (fpt_kernel / bpt_kernel) whatever the slab thickness
     int fp_variant = 0, bp_variant = 0;
+    int bp_xb = 0;                  // x-blocks per CTA of bpt_kernel: 0 = by slab thickness, 2 or 8 (ttv_set_option "bp_xb")
 
     double read_red(int slot) {
         double v; TTV_CUDA(cudaMemcpyAsync(&v, d_red + slot, sizeof(double), cudaMemcpyDeviceToHost, st)); sync();
@@ -623,8 +640,15 @@ public:
     }
     void zero_red(int slot) { TTV_CUDA(cudaMemsetAsync(d_red + slot, 0, sizeof(double), st)); }
 
+    // a collective needs the communicator of ttv_comm_init; slab engines of one process (ttv_set_rank +
+    // p2p_attach_local) have none and must not reach NCCL with a null handle
+    void need_comm(const char* what) const {
+        if (nranks > 1 && !comm) throw CudaError(std::string(what) + ": this slab engine has no communicator (ttv_comm_init was not called); "
+                                                 "collective results are not available in same-process slab mode");
+    }
     double allreduce_sum(double v) {
         if (nranks <= 1) return v;
+        need_comm("all-reduce");
         // host scalar -> device slot 15 -> all-reduce -> host
         TTV_CUDA(cudaMemcpyAsync(d_red + 15, &v, sizeof(double), cudaMemcpyHostToDevice, st));
         Nccl& n = Nccl::get();
@@ -739,6 +763,7 @@ public:
     // send slice `xs` of `src` to rank `to`, receive a plane from rank `from` (either may be -1)
     // ds/de: element stride / offset of the transferred layout (1/0 plain plane, 4/e ghost cells)
     void exchange(const float* src, int xs, int to, float* sendbuf, int from, float* recvbuf, int ds = 1, int de = 0) {
+        need_comm("halo exchange");
         Nccl& n = Nccl::get();
         const int64_t M = (int64_t)N * N;
         ProfScope ps(*this, PF_HALO);
@@ -790,14 +815,22 @@ public:
         if (d_err) TTV_CUDA(cudaMemcpyAsync(h_red + 16, d_err, 4 * sizeof(int), cudaMemcpyDeviceToHost, st));
         TTV_CUDA(cudaEventRecord(ev_red, st));
     }
+    void err_post() {
+        if (d_err) TTV_CUDA(cudaMemcpyAsync(h_red + 16, d_err, 4 * sizeof(int), cudaMemcpyDeviceToHost, st));
+        TTV_CUDA(cudaEventRecord(ev_red, st));
+    }
     double red_wait(int slot) {
         TTV_CUDA(cudaEventSynchronize(ev_red));
-        const int* err = reinterpret_cast<const int*>(h_red + 16);
-        if (err[0]) throw CudaError("timed out waiting for a neighbouring rank's halo epoch (peer-memory hand-off): rank " + std::to_string(rank) +
-                                    " side " + std::to_string(err[1]) + " flag " + std::to_string(err[2]) + " wanted " + std::to_string(err[3]));
+        int* err = reinterpret_cast<int*>(h_red + 16);
+        if (err[0]) {
+            const int e1 = err[1], e2 = err[2], e3 = err[3];
+            err[0] = 0;                                                   // reported once: later calls start clean
+            TTV_CUDA(cudaMemsetAsync(d_err, 0, 4 * sizeof(int), st));
+            throw CudaError("timed out waiting for a neighbouring rank's halo epoch (peer-memory hand-off): rank " + std::to_string(rank) +
+                            " side " + std::to_string(e1) + " flag " + std::to_string(e2) + " wanted " + std::to_string(e3));
+        }
         return h_red[slot];
     }
-
     // one tiled FGP launch (ttv_fgp.cuh); mode FGP_FIRST ignores P, FGP_FINAL writes D to `out`
     bool fgp_tiled = true;
     // rows per j-segment: trade the 2 redundant rows per segment against whole waves of CTAs on the SMs
@@ -859,16 +892,10 @@ public:
     float tv_fgp(int iter, float lambda) {
         use();
         const size_t n = vol_elems();
-        // every allocation first: cudaMalloc may synchronise the device, which must not happen while a
-        // wait kernel of this call spins on a neighbour's epoch
-        bool fresh = !scratch.ok();
+        // allocations: done by prealloc_tv() when the engine joined a sharded volume; a single-GPU engine allocates
+        // lazily here (nothing spins on it)
         if (!scratch.ok()) scratch.alloc(n);
-        for (int i = 0; i < 6; ++i) if (!P[i].ok() && iter > 1) { P[i].alloc(n); fresh = true; }
-        // ... and not on a NEIGHBOUR either: with peer access enabled a cudaMalloc maps the new memory on the peer
-        // devices, which can wait for a peer GPU that is itself spinning on this rank's epoch (seen at 2048^3 on
-        // 8 GPUs, 7 x 4 GiB allocated in the first call).  Every rank allocates in the same call, so one
-        // all-reduce here means "all ranks have finished allocating" before any rank starts to spin.
-        if (fresh && nranks > 1 && comm) (void)allreduce_sum(0.0);
+        for (int i = 0; i < 6; ++i) if (!P[i].ok() && iter > 1) P[i].alloc(n);
         // slice 0 of the right neighbour (ring): serves the periodic TV value, the TV map and -- on all but the
         // last rank -- the non-periodic FGP chain (`in` is constant over the sweeps): one exchange per call
         const float* hn = nullptr;
@@ -888,7 +915,6 @@ public:
         } else if (nranks > 1) { exchange(recon.p, 0, (rank - 1 + nranks) % nranks, ghost(0), (rank + 1) % nranks, ghost(1), 4, 0); hn = ghost(1); }
         tv_value_async(recon.p, 0, hn, 4);
         red_post(0);
-        if (!scratch.ok()) scratch.alloc(n);
         dim3 grid((N + TV_KSEG - 1) / TV_KSEG, (N + TV_WARPS - 1) / TV_WARPS, nxb);
         if (iter <= 0) {
             const int64_t rows = (int64_t)nxb * N;
@@ -896,7 +922,6 @@ public:
             std::swap(recon.p, scratch.p);
             return (float)red_wait(0);
         }
-        for (int i = 0; i < 6; ++i) if (!P[i].ok() && iter > 1) P[i].alloc(n);
         FgpParams p;
         p.in = recon.p; p.lambda = lambda; p.multip = 1.0f / (26.0f * lambda); p.d = dims();
         p.hl_P1 = p.hr_in = p.hr_P1 = p.hr_P2 = p.hr_P3 = nullptr;
@@ -976,8 +1001,11 @@ public:
             }
             TTV_LAUNCH_CHECK();
         }
-        std::swap(recon.p, scratch.p);   // the volume is replaced by the last D (tv_fgp.cu:272)
+        // peer-memory hand-off: an epoch time-out inside THIS call's sweeps must fail this call (the sweeps went on with
+        // stale ghost planes), so the error word is fetched again behind the last sweep; the volume is left untouched then
+        if (p2p) err_post();
         const float tv0 = (float)red_wait(0);
+        std::swap(recon.p, scratch.p);   // the volume is replaced by the last D (tv_fgp.cu:272)
         return tv0;
     }
 
@@ -1044,6 +1072,7 @@ public:
         int bits = r2 >= 0 ? r2 : r2 ^ 0x7FFFFFFF;
         float f; std::memcpy(&f, &bits, 4);
         if (nranks > 1) {
+            need_comm("max all-reduce");
             float* slot = reinterpret_cast<float*>(d_red + 14);
             TTV_CUDA(cudaMemcpyAsync(slot, &f, sizeof(float), cudaMemcpyHostToDevice, st));
             Nccl& nc = Nccl::get();
