@@ -10,7 +10,38 @@ GEOMS = {
     # name: (Nslice, Nray, angles_deg)
     "A": (34, 32, np.linspace(-90.0, 90.0, 12, endpoint=False)),
     "B": (3, 80, np.concatenate([np.arange(-70.0, 72.0, 5.0), [-90.0, -45.0, 0.0, 45.0, 89.5]])),
+    # three x-blocks (the last one ragged), five FGP k-tiles, three 64-detector groups, 9 x 9 BP tiles: every tiling
+    # dimension of the CUDA kernels is crossed at least twice.  Goldens of this geometry are DIGESTS (see digest()).
+    "C": (70, 136, np.linspace(-75.0, 75.0, 45)),
 }
+# geometries whose goldens hold selected slices + full-array norms instead of whole volumes (fixture size), and the
+# scenarios generated for them (FBP / CGLS / KL are covered by the small geometries)
+DIGEST_SLICES = {"C": [0, 31, 32, 63, 64, 69]}
+BIG_SCENARIOS = ("fp", "sirt", "sart", "kl_bp", "tv", "gd10", "fista", "asd", "misc")
+
+
+def scenarios_for(geom):
+    return {k: v for k, v in SCENARIOS.items() if geom not in DIGEST_SLICES or k in BIG_SCENARIOS}
+
+
+def digest(geom, out):
+    """Golden form of a scenario result for a DIGEST geometry: arrays indexed by slice keep only the slices of
+    DIGEST_SLICES (bit-exact float32) plus the float64 L2 norm and sum of the WHOLE array; scalars are kept."""
+    if geom not in DIGEST_SLICES:
+        return out
+    nx = GEOMS[geom][0]
+    idx = np.asarray(DIGEST_SLICES[geom])
+    res = {}
+    for k, v in out.items():
+        a = np.asarray(v)
+        if a.ndim >= 2 and a.shape[0] == nx:
+            res[k] = np.ascontiguousarray(a[idx])
+            res[k + "__idx"] = idx
+            res[k + "__norm"] = np.float64(np.linalg.norm(a.astype(np.float64).ravel()))
+            res[k + "__sum"] = np.float64(a.astype(np.float64).sum())
+        else:
+            res[k] = a
+    return res
 
 
 def angles_rad(geom):
@@ -109,6 +140,14 @@ def sc_tv(eng, inp, nx):
     eng.tv_fgp(0, 0.1)
     out["tvmap"] = volume(eng, nx)
     return out
+
+
+def sc_gd10(eng, inp, nx):
+    """TV-GD alone, ten inner iterations (tv_gd.cu:141-218): pins the gradient kernel at a realistic size."""
+    eng.restart_recon()
+    load_volume(eng, inp["noisy"])
+    ret = np.float32(eng.tv_gd(10, 0.5))
+    return {"gd10_ret": ret, "gd10": volume(eng, nx)}
 
 
 def sc_fista(eng, inp, nx, niter=5, lam=0.1, ntv=10):
@@ -216,7 +255,7 @@ def sc_fbp(eng, inp, nx):
 SCENARIOS = {
     "cgls": sc_cgls, "fbp": sc_fbp,
     "fp": sc_fp, "sirt": sc_sirt, "sart": sc_sart, "kl": sc_kl, "kl_bp": sc_kl_bp, "tv": sc_tv,
-    "fista": sc_fista, "fista_nomom": sc_fista_nomom, "asd": sc_asd, "misc": sc_misc,
+    "fista": sc_fista, "fista_nomom": sc_fista_nomom, "asd": sc_asd, "misc": sc_misc, "gd10": sc_gd10,
 }
 
 # tolerances (relative L2 for arrays, relative for scalars), from BASELINE.json north_star:
@@ -225,15 +264,21 @@ TOL = {
     ("fp", "g"): 1e-5, ("misc", "b"): 1e-5,
     ("sirt", "recon1"): 1e-5,          # = C * BP(R * b): one application of the back projector
     ("kl_bp", "recon"): 1e-5,
-    # ASD-POCS alternates SART with TV-GD steps x -= dPOCS*g/|g| whose gradient terms v/sqrt(1e-6+|grad|^2)
-    # amplify float32 rounding noise 1000x wherever the volume is flat (the clamped-to-zero background), and
-    # the reference's TV-GD kernel additionally reads out of bounds (see gd_mask).  Two correct float32
-    # implementations therefore agree on the volume only to ~1e-2 on these tiny cases; the scalars the
-    # algorithm steers by (dd, dp, tv) still agree to 1e-4.
+    # ASD-POCS alternates SART with TV-GD steps x -= dPOCS*g/|g| whose gradient terms v/sqrt(1e-6+|grad|^2) amplify
+    # float32 rounding noise ~1000x wherever the volume is flat (the clamped-to-zero background).  Measured on a B200
+    # (profiles/r2_parity_table.txt): TV-GD ALONE is bit-identical to the reference at a realistic size (C/gd10 and
+    # C/tv/gd: relative L2 = 0, unmasked) and every scalar the algorithm steers by (dd, dp, tv) agrees to <= 6e-6 at C;
+    # the ASD-POCS VOLUME differs by 1.7e-3 at C although its two halves agree to 8e-7 (SART) and 0 (TV-GD).  That is
+    # the algorithm's own conditioning: two runs of the UNMODIFIED reference on the same inputs differ by 6.8e-3 (A) and
+    # 2.5e-3 (B) in `recon` (tests/golden/spread_*_asd.npz; its TV-GD kernel reads out of bounds on small grids), and the
+    # reference fed with inputs perturbed by one ulp moves by spread_C_asd.npz:recon_sens.  The volume tolerance is
+    # therefore "within the reference's own spread", the scalars keep north_star's 1e-4 at C.
     ("asd", "recon"): 2e-2,
-    # the out-of-bounds reads make the reference's own ASD-POCS scalars vary from run to run at the 1e-4 level
-    # (two golden generations on the same B200: B/asd/dp 6.8e-5 and 1.08e-4 from the same oracle)
-    ("asd", "dp"): 5e-4, ("asd", "tv"): 5e-4, ("asd", "dd"): 5e-4,
+    ("C", "asd", "recon"): 5e-3,
+    # small grids: the out-of-bounds reads make the reference's own ASD-POCS scalars vary from run to run
+    # (spread_A_asd / spread_B_asd: 1.9e-5; an earlier generation on the same B200: 1.08e-4)
+    ("A", "asd", "dp"): 5e-4, ("A", "asd", "tv"): 5e-4, ("A", "asd", "dd"): 5e-4,
+    ("B", "asd", "dp"): 5e-4, ("B", "asd", "tv"): 5e-4, ("B", "asd", "dd"): 5e-4,
 }
 DEFAULT_TOL = 1e-4
 
@@ -261,18 +306,44 @@ def rel_l2(a, b):
     return d / n if n > 0 else d
 
 
-def compare(scn, got, want):
-    """-> list of (key, error, tolerance, ok)."""
+GD_MASKED = {("tv", "gd"): 5, ("gd10", "gd10"): 10}      # (scenario, key) -> inner TV-GD iterations behind the array
+# geometries compared WITHOUT the mask: at a realistic size the reference's out-of-bounds reads land in zeroed memory of
+# its own allocation and the whole TV-GD volume agrees (measured: relative L2 = 0 at C); the 34x32^2 / 3x80^2 grids
+# read whatever precedes the buffer
+GD_UNMASKED_GEOMS = ("C",)
+
+
+def tol_for(geom, scn, k):
+    return TOL.get((geom, scn, k), TOL.get((scn, k), DEFAULT_TOL))
+
+
+def compare(scn, got, want, geom=None):
+    """-> list of (key, error, tolerance, ok).  `want` may be a digest (see digest()): then the stored slices are
+    compared and the full-array norm must agree to the same tolerance."""
     rows = []
     for k in sorted(want):
+        if "__" in k:
+            continue
         if k not in got:
             rows.append((k, float("nan"), 0.0, False))
             continue
-        tol = TOL.get((scn, k), DEFAULT_TOL)
-        if (scn, k) == ("tv", "gd"):
-            m = gd_mask(np.shape(want[k]))
-            e = rel_l2(np.asarray(got[k])[m], np.asarray(want[k])[m])
+        tol = tol_for(geom, scn, k)
+        g, w = np.asarray(got[k]), np.asarray(want[k])
+        idx = want.get(k + "__idx")
+        full_shape = g.shape
+        if idx is not None:
+            if g.shape[0] != len(idx):
+                g = g[np.asarray(idx)]
+        if (scn, k) in GD_MASKED and geom not in GD_UNMASKED_GEOMS:
+            m = gd_mask(full_shape if idx is not None else w.shape, GD_MASKED[(scn, k)])
+            if idx is not None:
+                m = m[np.asarray(idx)]
+            e = rel_l2(g[m], w[m])
         else:
-            e = rel_l2(got[k], want[k])
+            e = rel_l2(g, w)
+            if idx is not None and np.asarray(got[k]).shape[0] != len(idx):
+                nrm = float(np.linalg.norm(np.asarray(got[k], np.float64).ravel()))
+                wn = float(want[k + "__norm"])
+                e = max(e, abs(nrm - wn) / wn if wn > 0 else abs(nrm))
         rows.append((k, float(e), tol, bool(e <= tol)))
     return rows

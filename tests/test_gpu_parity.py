@@ -20,8 +20,7 @@ def _oracle_for(orc, eng, nx, n, ang):
     return orc.Oracle(nx, n, ang, quant=1, cosv=cosv, sinv=sinv)
 
 
-@pytest.mark.parametrize("geom", list(S.GEOMS))
-@pytest.mark.parametrize("scn", list(S.SCENARIOS))
+@pytest.mark.parametrize("geom,scn", [(g, s) for g in S.GEOMS for s in S.scenarios_for(g)])
 def test_cuda_matches_oracle(ttv, orc, geom, scn):
     nx, n, _ = S.GEOMS[geom]
     ang = S.angles_rad(geom)
@@ -32,7 +31,7 @@ def test_cuda_matches_oracle(ttv, orc, geom, scn):
     eng = ttv.tomoengine(nx, n, ang)
     want = S.SCENARIOS[scn](_oracle_for(orc, eng, nx, n, ang), inp, nx)
     got = S.SCENARIOS[scn](eng, inp, nx)
-    bad = [r for r in S.compare(scn, got, want) if not r[3]]
+    bad = [r for r in S.compare(scn, got, want, geom) if not r[3]]
     assert not bad, bad
 
 
@@ -42,7 +41,7 @@ def test_cuda_matches_reference_goldens(ttv, geom, scn):
     nx, n, _ = S.GEOMS[geom]
     eng = ttv.tomoengine(nx, n, inp["angles"])
     got = S.SCENARIOS[scn](eng, inp, nx)
-    bad = [r for r in S.compare(scn, got, want) if not r[3]]
+    bad = [r for r in S.compare(scn, got, want, geom) if not r[3]]
     assert not bad, bad
 
 

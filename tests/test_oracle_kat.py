@@ -226,5 +226,5 @@ def test_oracle_matches_reference_goldens(orc, geom, scn):
     nx, n, _ = S.GEOMS[geom]
     eng = orc.Oracle(nx, n, inp["angles"], quant=1, cosv=inp["cosv"], sinv=inp["sinv"])
     got = S.SCENARIOS[scn](eng, inp, nx)
-    bad = [r for r in S.compare(scn, got, want) if not r[3]]
+    bad = [r for r in S.compare(scn, got, want, geom) if not r[3]]
     assert not bad, bad
