@@ -302,6 +302,8 @@ def run_ours(args):
         "fp": V + 2 * S,                                        # read x, read b, write residual (fused SIRT residual)
         "bp": S + 2 * V,                                        # read residual, read x, write x (fused SIRT update)
         "fgp_first": 4 * V, "fgp_sweep": 7 * V, "fgp_final": 5 * V, "tv": V, "momentum": 3 * V,
+        # two sweeps per launch (ttv_fgp2.cuh): the pair moves what ONE sweep of its kind moves
+        "fgp2_first": 4 * V, "fgp2_sweep": 7 * V, "fgp2_final": 5 * V,
     }
     groups = {}
     for g, (tot, cnt) in prof.items():
@@ -321,7 +323,8 @@ def run_ours(args):
     dom = max(hbm_groups, key=lambda g: prof[g][0]) if hbm_groups else None
     roof = None
     if dom:
-        roof = {"kernel": {"fgp_sweep": "fgp_tile_kernel<SWEEP>", "fgp_first": "fgp_tile_kernel<FIRST>", "fgp_final": "fgp_tile_kernel<FINAL>"}.get(dom, dom),
+        roof = {"kernel": {"fgp_sweep": "fgp_tile_kernel<SWEEP>", "fgp_first": "fgp_tile_kernel<FIRST>", "fgp_final": "fgp_tile_kernel<FINAL>",
+                           "fgp2_sweep": "fgp2_kernel<SWEEP,SWEEP>", "fgp2_first": "fgp2_kernel<FIRST,SWEEP>", "fgp2_final": "fgp2_kernel<SWEEP,FINAL>"}.get(dom, dom),
                 "bound": "hbm", "achieved": groups[dom]["achieved_gbs"], "peak": pk["hbm_gbs"], "unit": "GB/s",
                 "frac": groups[dom]["frac_of_hbm_peak"], "traffic": traffic_512().get(dom) if (n, na, world) == (512, 180, 1) else None, "peak_kind": pk_kind,
                 "algorithmic_bytes_per_launch": alg_bytes[dom], "share_of_step": groups[dom]["share_of_step"],

@@ -188,17 +188,22 @@ int ttv_set_model_projections(ttv_handle h, const float* g, int rows, int cols);
 int ttv_time_kernel(ttv_handle h, const char* name, int reps, int arg_i, float arg_f, float* ms);
 /* per-kernel-group CUDA-event timing on the engine's stream: enable (resets the counters), run, then
  * read total milliseconds and launch count per group.  groups: fp, bp, fgp_first, fgp_sweep, fgp_final,
- * tv, momentum, tvgd_grad, tvgd_update, reduce, elementwise, sart_fp, sart_bp, io, halo. */
+ * tv, momentum, tvgd_grad, tvgd_update, reduce, elementwise, sart_fp, sart_bp, io, halo, fgp2_first, fgp2_sweep,
+ * fgp2_final (two-sweep launches). */
 int ttv_profile(ttv_handle h, int enable);
 int ttv_profile_get(ttv_handle h, const char* group, double* total_ms, long long* count);
 /* CUDA events on the engine's stream around an arbitrary sequence of calls */
 int ttv_timer_start(ttv_handle h);
 int ttv_timer_stop(ttv_handle h, float* ms);
 /* implementation switches for A/B tests: "fgp_tiled" (1 = TMA-tiled TV-FGP sweep, 0 = first-generation kernel);
- * "fp_variant" (0 = default, 1 = experimental parity-register reuse, 8 = experimental 8-slices-per-lane kernel) and "bp_variant" (4 = default, 5 / 8 / 9 =
- * experimental 8-slices-per-lane kernels with register reuse): experimental values are not validated yet and
- * are never selected by default. */
+ * "fgp_fuse" (1 = two FGP sweeps per launch on a single-volume engine, ttv_fgp2.cuh; 0 = one launch per sweep);
+ * "fp_variant" / "bp_variant" (0 = by slab thickness, 1 = classic fp_kernel / bp_kernel, 2 = table-driven fpt_kernel /
+ * bpt_kernel); "bp_xb" (x-blocks per CTA of bpt_kernel: 0 = by slab thickness, 2, 8).  Every value selects a kernel the
+ * GPU tests validate (all variants are bit-identical to each other). */
 int ttv_set_option(ttv_handle h, const char* name, int value);
+/* self-test of the inlined 1/sqrt used by the TV-FGP projection step: number of n pseudo-random arguments > 1 whose result
+ * differs from IEEE div(1, sqrt(x)) (the reference's expression, tv_fgp.cu:106); must be 0 */
+int ttv_selftest_invsqrt(ttv_handle h, unsigned long long n, unsigned seed, unsigned long long* mismatches);
 /* number of kernel launches issued by this engine so far */
 int ttv_launch_count(ttv_handle h, long long* n);
 /* algorithmic geometry facts for the roofline: bytes of one volume (V) and one sinogram (S) */

@@ -325,3 +325,37 @@ def test_multigpuengine_without_process_group_is_a_single_gpu_engine(ttv):
     assert np.array_equal(outs[0], outs[1])
     m = ttv.multigpuengine(nx, n, ang)
     assert m.is_multi_gpu_enabled() is False and len(m.get_gpu_ids()) == 1 and m.global_nslice == nx
+
+
+@pytest.mark.parametrize("nx,n,it", [(1, 5, 2), (33, 63, 4), (70, 100, 3), (64, 129, 2), (40, 31, 5), (32, 30, 10), (96, 66, 6),
+                                     (65, 58, 7), (31, 29, 4), (97, 87, 10), (3, 200, 4)])
+def test_fgp_two_sweeps_per_launch_is_bit_identical(ttv, nx, n, it):
+    """fgp2_kernel (ttv_fgp2.cuh: two TV-FGP sweeps per launch, halo slices of the neighbouring x-blocks re-computed by a
+    halo warp) against one launch per sweep: same operations in the same order, so the TV value, the dual variables'
+    effect and the denoised volume are bit-identical -- for even and odd sweep counts (FIRST+SWEEP, SWEEP+SWEEP,
+    SWEEP+FINAL, FIRST+FINAL pairs and a trailing single FINAL), ragged Nx, N below / across the 29-column k-tile and the
+    j-segment."""
+    rng = np.random.default_rng(nx * 977 + n * 13 + it)
+    v = (0.5 + 0.4 * rng.standard_normal((nx, n, n))).astype(np.float32)       # has negative voxels too
+    ang = np.zeros(2, np.float32)
+    outs = []
+    for fuse in (1, 0):
+        eng = ttv.tomoengine(nx, n, ang)
+        eng.set_option("fgp_fuse", fuse)
+        eng.set_recon_all(v)
+        l0 = eng.launch_count()
+        tv0 = eng.tv_fgp(it, 0.1)
+        outs.append((tv0, eng.get_recon_all(), eng.launch_count() - l0))
+    assert outs[0][2] < outs[1][2]                       # the fused path really ran (fewer launches)
+    assert outs[0][0] == outs[1][0]
+    assert np.array_equal(outs[0][1], outs[1][1])
+    # a second call on the result (dual buffers are reused) stays identical too
+    assert not np.isnan(outs[0][1]).any()
+
+
+def test_inlined_inverse_sqrt_equals_ieee_div_of_sqrt(ttv):
+    """The projection step's 1/sqrt(den) (ttv_fgp2.cuh: inv_sqrt_ieee, the fast paths of IEEE sqrt and division without their
+    out-of-range fall-backs) against __fdiv_rn(1, __fsqrt_rn(den)), the reference's expression (tv_fgp.cu:106), on 2^26
+    arguments in (1, 2^64)."""
+    eng = ttv.tomoengine(1, 8, np.zeros(2, np.float32))
+    assert eng.selftest_invsqrt(1 << 26, 12345) == 0

@@ -326,6 +326,7 @@ int ttv_set_option(ttv_handle h, const char* name, int value) {
     Engine& e = E(h);
     const std::string nm = name ? name : "";
     if (nm == "fgp_tiled") e.fgp_tiled = value != 0;
+    else if (nm == "fgp_fuse") e.fgp_fuse = value != 0;
     else if (nm == "fp_variant") {
         if (value < 0 || value > 2) throw CudaError("ttv_set_option: fp_variant must be 0 (by slab thickness), 1 (classic) or 2 (table-driven)");
         e.fp_variant = value;
@@ -339,6 +340,20 @@ int ttv_set_option(ttv_handle h, const char* name, int value) {
         e.bp_xb = value;
     }
     else throw CudaError("ttv_set_option: unknown option '" + nm + "'");
+    TTV_CATCH
+}
+int ttv_selftest_invsqrt(ttv_handle h, unsigned long long n, unsigned seed, unsigned long long* mismatches) {
+    TTV_TRY
+    Engine& e = E(h);
+    e.use();
+    unsigned long long* d = nullptr;
+    TTV_CUDA(cudaMalloc(&d, sizeof(unsigned long long)));
+    TTV_CUDA(cudaMemsetAsync(d, 0, sizeof(unsigned long long), e.st));
+    invsqrt_selftest_kernel<<<592, 256, 0, e.st>>>(n, seed, d); ++e.launches;
+    TTV_LAUNCH_CHECK();
+    TTV_CUDA(cudaMemcpyAsync(mismatches, d, sizeof(unsigned long long), cudaMemcpyDeviceToHost, e.st));
+    e.sync();
+    cudaFree(d);
     TTV_CATCH
 }
 int ttv_launch_count(ttv_handle h, long long* n) { TTV_TRY *n = E(h).launches; TTV_CATCH }
@@ -380,6 +395,9 @@ int ttv_time_kernel(ttv_handle h, const char* name, int reps, int arg_i, float a
         else if (nm == "fgp_sweep") e.fgp_launch(FGP_SWEEP, fp, nullptr);
         else if (nm == "fgp_first") e.fgp_launch(FGP_FIRST, fp, nullptr);
         else if (nm == "fgp_final") e.fgp_launch(FGP_FINAL, fp, e.scratch.p);
+        else if (nm == "fgp2_sweep") e.fgp2_launch(FGP_SWEEP, FGP_SWEEP, fp, nullptr);
+        else if (nm == "fgp2_first") e.fgp2_launch(FGP_FIRST, FGP_SWEEP, fp, nullptr);
+        else if (nm == "fgp2_final") e.fgp2_launch(FGP_SWEEP, FGP_FINAL, fp, e.scratch.p);
         else if (nm == "tv_v1") { tv_value_kernel<<<(unsigned)((rows + 7) / 8), 256, 0, e.st>>>(e.recon.p, e.dims(), nullptr, 1, e.d_red); ++e.launches; }
         else if (nm == "tv") { tv_value_tiled_kernel<<<dim3(gsw.x, (e.N + 7) / 8, e.nxb), 256, 0, e.st>>>(e.recon.p, e.dims(), nullptr, 1, e.d_red); ++e.launches; }
         else if (nm == "momentum") { momentum_kernel<<<ew_blocks(n / 4), 256, 0, e.st>>>(reinterpret_cast<float4*>(e.scratch.p), reinterpret_cast<float4*>(e.yk.p), reinterpret_cast<float4*>(e.recon_old.p), 0.5f, n / 4); ++e.launches; }

@@ -13,6 +13,7 @@
 #include "ttv_bpt.cuh"
 #include "ttv_tv.cuh"
 #include "ttv_fgp.cuh"
+#include "ttv_fgp2.cuh"
 #include "ttv_elem.cuh"
 #include <vector>
 #include <string>
@@ -183,10 +184,10 @@ struct DBuf {
 // Per-kernel-group timing with CUDA events on the engine's stream (bench.py's roofline numbers are
 // measured live inside the timed region, not under a profiler).
 enum ProfId { PF_FP = 0, PF_BP, PF_FGP_FIRST, PF_FGP_SWEEP, PF_FGP_FINAL, PF_TV, PF_MOMENTUM, PF_TVGD_GRAD, PF_TVGD_UPD,
-              PF_REDUCE, PF_EW, PF_SART_FP, PF_SART_BP, PF_IO, PF_HALO, PF_COUNT };
+              PF_REDUCE, PF_EW, PF_SART_FP, PF_SART_BP, PF_IO, PF_HALO, PF_FGP2_FIRST, PF_FGP2_SWEEP, PF_FGP2_FINAL, PF_COUNT };
 inline const char* prof_name(int i) {
     static const char* nm[PF_COUNT] = {"fp", "bp", "fgp_first", "fgp_sweep", "fgp_final", "tv", "momentum", "tvgd_grad", "tvgd_update",
-                                       "reduce", "elementwise", "sart_fp", "sart_bp", "io", "halo"};
+                                       "reduce", "elementwise", "sart_fp", "sart_bp", "io", "halo", "fgp2_first", "fgp2_sweep", "fgp2_final"};
     return nm[i];
 }
 
@@ -354,6 +355,10 @@ public:
         TTV_CUDA(cudaFuncSetAttribute(fgp_tile_kernel<FGP_SWEEP, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)FGP_SMEM));
         TTV_CUDA(cudaFuncSetAttribute(fgp_tile_kernel<FGP_FIRST, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)FGP_SMEM));
         TTV_CUDA(cudaFuncSetAttribute(fgp_tile_kernel<FGP_FINAL, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)FGP_SMEM));
+        TTV_CUDA(cudaFuncSetAttribute(fgp2_kernel<FGP_SWEEP, FGP_SWEEP>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)F2Cfg<FGP_SWEEP>::SMEM));
+        TTV_CUDA(cudaFuncSetAttribute(fgp2_kernel<FGP_SWEEP, FGP_FINAL>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)F2Cfg<FGP_SWEEP>::SMEM));
+        TTV_CUDA(cudaFuncSetAttribute(fgp2_kernel<FGP_FIRST, FGP_SWEEP>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)F2Cfg<FGP_FIRST>::SMEM));
+        TTV_CUDA(cudaFuncSetAttribute(fgp2_kernel<FGP_FIRST, FGP_FINAL>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)F2Cfg<FGP_FIRST>::SMEM));
         if (nang > 0) set_angles(ang, nang);
     }
     ~Engine() {
@@ -888,6 +893,44 @@ public:
         ++launches;
     }
 
+    // two sweeps per launch (ttv_fgp2.cuh): ma = FGP_FIRST / FGP_SWEEP (first sweep of the pair), mb = FGP_SWEEP / FGP_FINAL
+    bool fgp_fuse = true;
+    int fgp2_seg() {
+        if (N < 48) return (N + 1) & ~1;
+        if (!sm_count) { cudaDeviceProp pr; TTV_CUDA(cudaGetDeviceProperties(&pr, device)); sm_count = pr.multiProcessorCount; }
+        const int kt = (N + F2_TKO - 1) / F2_TKO;
+        int best = 64; double beff = -1.0;
+        for (int seg = 32; seg <= 256; seg += 2) {
+            const int z = (N + seg - 1) / seg;
+            const double waves = (double)nxb * kt * z / sm_count;
+            // whole waves of one-CTA-per-SM blocks x the share of staged rows that are outputs (4 redundant rows + 2 rows of pipeline fill per segment)
+            const double eff = waves / std::ceil(waves) * ((double)N / ((double)z * (seg + 6)));
+            if (eff > beff + 1e-9) { beff = eff; best = seg; }
+        }
+        return best;
+    }
+    void fgp2_launch(int ma, int mb, const FgpParams& p, float* out) {
+        F2Maps tm;
+        tm.in = make_tmap(p.in, N, N, nxb, F2_CW, 2);
+        tm.inh = make_tmap(p.in, N, N, nxb, F2_CW, 2, 4);
+        if (ma == FGP_FIRST) { tm.p1 = tm.p2 = tm.p3 = tm.in; tm.p1h = tm.p2h = tm.p3h = tm.inh; }
+        else {
+            tm.p1 = make_tmap(p.P1, N, N, nxb, F2_CW, 2); tm.p1h = make_tmap(p.P1, N, N, nxb, F2_CW, 2, 4);
+            tm.p2 = make_tmap(p.P2, N, N, nxb, F2_CW, 2); tm.p2h = make_tmap(p.P2, N, N, nxb, F2_CW, 2, 4);
+            tm.p3 = make_tmap(p.P3, N, N, nxb, F2_CW, 2); tm.p3h = make_tmap(p.P3, N, N, nxb, F2_CW, 2, 4);
+        }
+        const int seg = fgp2_seg();
+        dim3 grid(nxb, (N + F2_TKO - 1) / F2_TKO, (N + seg - 1) / seg);
+        if (ma == FGP_FIRST) {
+            if (mb == FGP_FINAL) fgp2_kernel<FGP_FIRST, FGP_FINAL><<<grid, F2_THREADS, F2Cfg<FGP_FIRST>::SMEM, st>>>(tm, p, out, seg);
+            else fgp2_kernel<FGP_FIRST, FGP_SWEEP><<<grid, F2_THREADS, F2Cfg<FGP_FIRST>::SMEM, st>>>(tm, p, out, seg);
+        } else {
+            if (mb == FGP_FINAL) fgp2_kernel<FGP_SWEEP, FGP_FINAL><<<grid, F2_THREADS, F2Cfg<FGP_SWEEP>::SMEM, st>>>(tm, p, out, seg);
+            else fgp2_kernel<FGP_SWEEP, FGP_SWEEP><<<grid, F2_THREADS, F2Cfg<FGP_SWEEP>::SMEM, st>>>(tm, p, out, seg);
+        }
+        ++launches;
+    }
+
     // cuda_tv_fgp_3D, tv_fgp.cu:192-281.  Returns TV of the input.
     float tv_fgp(int iter, float lambda) {
         use();
@@ -929,8 +972,25 @@ public:
         const bool has_left = nranks > 1 && rank > 0, has_right = nranks > 1 && rank < nranks - 1;
         if (has_right) p.hr_in = hn;
         int cur = 0;   // P[cur*3 ..] holds the current dual variable
+        const bool fuse = fgp_fuse && fgp_tiled && nranks == 1 && iter >= 2;
         for (int it = 0; it < iter; ++it) {
             const bool first = (it == 0), last = (it == iter - 1);
+            if (fuse && it + 1 < iter) {
+                // sweeps it and it+1 in one launch (ttv_fgp2.cuh); an odd sweep count leaves the FINAL sweep to the single-sweep kernel below
+                const bool last2 = (it + 1 == iter - 1);
+                if (!first) { p.P1 = P[cur * 3 + 0].p; p.P2 = P[cur * 3 + 1].p; p.P3 = P[cur * 3 + 2].p; }
+                else { p.P1 = p.P2 = p.P3 = nullptr; }
+                const int nxt = first ? 0 : 1 - cur;
+                p.Q1 = P[nxt * 3 + 0].p; p.Q2 = P[nxt * 3 + 1].p; p.Q3 = P[nxt * 3 + 2].p;
+                {
+                    ProfScope ps(*this, first ? PF_FGP2_FIRST : last2 ? PF_FGP2_FINAL : PF_FGP2_SWEEP);
+                    fgp2_launch(first ? FGP_FIRST : FGP_SWEEP, last2 ? FGP_FINAL : FGP_SWEEP, p, scratch.p);
+                }
+                TTV_LAUNCH_CHECK();
+                if (!last2) cur = nxt;
+                ++it;
+                continue;
+            }
             if (!first) {
                 p.P1 = P[cur * 3 + 0].p; p.P2 = P[cur * 3 + 1].p; p.P3 = P[cur * 3 + 2].p;
                 if (p2p) {

@@ -301,7 +301,7 @@ class tomoengine:
         return v.value
 
     PROFILE_GROUPS = ("fp", "bp", "fgp_first", "fgp_sweep", "fgp_final", "tv", "momentum", "tvgd_grad",
-                      "tvgd_update", "reduce", "elementwise", "sart_fp", "sart_bp", "io", "halo")
+                      "tvgd_update", "reduce", "elementwise", "sart_fp", "sart_bp", "io", "halo", "fgp2_first", "fgp2_sweep", "fgp2_final")
 
     def profile(self, enable=True):
         check(lib().ttv_profile(self._h, int(bool(enable))))
@@ -322,6 +322,11 @@ class tomoengine:
     def timer_stop(self):
         v = C.c_float(0)
         check(lib().ttv_timer_stop(self._h, C.byref(v)))
+        return v.value
+
+    def selftest_invsqrt(self, n=1 << 24, seed=1):
+        v = C.c_ulonglong(0)
+        check(lib().ttv_selftest_invsqrt(self._h, C.c_ulonglong(int(n)), C.c_uint(int(seed)), C.byref(v)))
         return v.value
 
     def launch_count(self):
