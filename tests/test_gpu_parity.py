@@ -131,12 +131,14 @@ def test_fgp_tiled_kernel_matches_oracle_and_first_generation(ttv, orc, nx, n, i
     assert S.rel_l2(outs[0][1], o.recon) <= 1e-6
 
 
-@pytest.mark.parametrize("nx,n,it", [(70, 96, 4), (64, 45, 3), (40, 130, 5)])
-def test_fgp_peer_memory_handoff_two_slabs_one_gpu(ttv, nx, n, it):
-    """The sharded TV-FGP path without NCCL: two slab engines in this process, attached to each other's
-    ghost-plane buffers (plain pointers instead of CUDA IPC handles), driven by one host thread each.  The
-    sweep kernels store their boundary slices into the neighbour's planes and hand over with epoch flags;
-    the result must equal the whole-volume engine bit for bit."""
+@pytest.mark.parametrize("nx,n,it,nr", [(70, 96, 4, 2), (64, 45, 3, 2), (40, 130, 5, 2), (35, 40, 10, 2), (66, 70, 6, 3), (100, 61, 4, 3), (7, 33, 8, 3)])
+def test_fgp_peer_memory_handoff_two_slabs_one_gpu(ttv, nx, n, it, nr):
+    """The sharded TV-FGP path without NCCL: two or three slab engines in this process, attached to each other's
+    ghost buffers (plain pointers instead of CUDA IPC handles), driven by one host thread each.  Odd sweep counts run one
+    launch per sweep (the kernels store their boundary slices into the neighbour's planes and hand over with epoch
+    flags); even counts run two sweeps per launch on two-slice-deep ghost cells pushed before every pair (a middle slab
+    has ghosts on both sides, a thin one is a single ragged x-block).  The result must equal the whole-volume engine
+    bit for bit."""
     import threading
     from tomo_tv_b200.phantom import slab_bounds
     rng = np.random.default_rng(nx + n)
@@ -147,28 +149,28 @@ def test_fgp_peer_memory_handoff_two_slabs_one_gpu(ttv, nx, n, it):
     tv_whole = [whole.tv_fgp(it, 0.1), whole.tv_fgp(2, 0.05)]
     ref = whole.get_recon_all()
     engs = []
-    for r in range(2):
-        f, c = slab_bounds(nx, 2, r)
+    for r in range(nr):
+        f, c = slab_bounds(nx, nr, r)
         e = ttv.tomoengine(c, n, ang, x_offset=f, nslice_global=nx)
-        e.set_rank(r, 2)
+        e.set_rank(r, nr)
         e.set_recon_all(v[f:f + c])
         engs.append(e)
-    engs[0].p2p_attach_local(engs[1], engs[1])
-    engs[1].p2p_attach_local(engs[0], engs[0])
-    tvs, errs = [None, None], []
+    for r in range(nr):          # ring neighbours, as sharded.setup_sharding attaches them
+        engs[r].p2p_attach_local(engs[(r - 1) % nr], engs[(r + 1) % nr])
+    tvs, errs = [None] * nr, []
 
     def work(r):
         try:
             tvs[r] = [engs[r].tv_fgp(it, 0.1), engs[r].tv_fgp(2, 0.05)]
         except Exception as ex:      # pragma: no cover
             errs.append(ex)
-    th = [threading.Thread(target=work, args=(r,)) for r in range(2)]
+    th = [threading.Thread(target=work, args=(r,)) for r in range(nr)]
     [t.start() for t in th]; [t.join() for t in th]
     assert not errs, errs
     got = np.concatenate([e.get_recon_all() for e in engs])
     assert np.array_equal(got, ref)
     for q in range(2):      # without a communicator each slab returns its partial TV
-        assert abs(tvs[0][q] + tvs[1][q] - tv_whole[q]) <= 1e-5 * abs(tv_whole[q])
+        assert abs(sum(t[q] for t in tvs) - tv_whole[q]) <= 1e-5 * abs(tv_whole[q])
 
 
 def test_momentum_and_reductions(ttv):
@@ -359,3 +361,34 @@ def test_inlined_inverse_sqrt_equals_ieee_div_of_sqrt(ttv):
     arguments in (1, 2^64)."""
     eng = ttv.tomoengine(1, 8, np.zeros(2, np.float32))
     assert eng.selftest_invsqrt(1 << 26, 12345) == 0
+
+
+@pytest.mark.parametrize("nx,n,na,order", [(5, 64, 12, "sequential"), (3, 300, 9, "sequential"), (2, 512, 14, "sequential"),
+                                           (37, 136, 20, "random"), (1, 40, 7, "sequential"), (9, 7, 5, "sequential")])
+def test_sart_cluster_kernel_matches_per_angle_kernels(ttv, orc, nx, n, na, order):
+    """sartc_kernel (ttv_sartc.cuh: slice resident in a cluster's distributed shared memory, one launch per pass, S = 4 / 2 / 1
+    slices per cluster) against the per-angle kernels of ttv_sart.cuh and the CPU oracle: same per-sample operations; the ray
+    sums are accumulated per band and combined in a fixed order, so the two agree to float32 rounding, not bit for bit."""
+    rng = np.random.default_rng(nx * 31 + n)
+    ang = np.deg2rad(np.sort(rng.uniform(-88, 88, na))).astype(np.float32)
+    b = rng.random((nx, na * n), dtype=np.float32) * 3
+    outs = []
+    for cl in (1, 0):
+        eng = ttv.tomoengine(nx, n, ang)
+        eng.set_option("sart_cluster", cl)
+        eng.set_tilt_series(b)
+        eng.initialize_SART(order)
+        eng.initialize_FP()
+        eng.restart_recon()
+        import ctypes
+        ctypes.CDLL("libc.so.6").srand(7)            # "random" order draws from rand() (tomoengine.cpp:164): same sequence for both runs
+        l0 = eng.launch_count()
+        eng.SART(0.7, 2)
+        outs.append((eng.get_recon_all(), eng.launch_count() - l0))
+    assert outs[0][1] == 1 and outs[1][1] == 4 * na           # one cluster launch against 2 launches per sub-iteration
+    assert S.rel_l2(outs[0][0], outs[1][0]) <= 2e-6
+    if order == "sequential":
+        o = _oracle_for(orc, eng, nx, n, ang)
+        o.set_tilt_series(b); o.initialize_SART("sequential"); o.restart_recon()
+        o.SART(0.7, 2)
+        assert S.rel_l2(outs[0][0], o.recon) <= 5e-6

@@ -204,3 +204,24 @@ def test_bp_detector_windows_hold_every_sample_of_the_tile(tx, ty, cw):
             cell = np.floor(fx * float(c) - fy * float(s) + float(off) - 0.5).astype(int) - w0
             lo, hi = min(lo, int(cell.min())), max(hi, int(cell.max()))
     assert lo >= 0 and hi + 1 <= cw - 2          # at least one spare cell for float32 rounding at either end
+
+
+def test_tomofusion_import_paths_resolve_to_this_package(ttv):
+    """The reference's import spellings (tomofusion/gpu/reconstructor.py:1-3, chemistry/reconstructor.py:1-2,
+    gpu/utils/__init__.py:2, gpu/simulator.py:1-2) work against the `tomofusion/` shim and name this package's classes."""
+    import tomofusion
+    from tomofusion.gpu.utils import tomoengine, multigpuengine
+    from tomofusion.gpu.reconstructor import TomoGPU, reconstructor
+    from tomofusion import pytvlib
+    from tomofusion.chemistry.utils import multimodal, multigpufusion
+    from tomofusion.chemistry.utils import fusion_helper as utils
+    from tomofusion.chemistry.reconstructor import ChemicalTomo
+    assert tomoengine.tomoengine is ttv.tomoengine and multigpuengine.multigpuengine is ttv.multigpuengine
+    assert multimodal is ttv.multimodal and multigpufusion.multigpufusion is ttv.multigpufusion
+    assert TomoGPU is ttv.TomoGPU and reconstructor is ttv.TomoGPU and ChemicalTomo is ttv.ChemicalTomo
+    assert pytvlib.wbp_filters() == ttv.pytvlib.wbp_filters()
+    assert utils.get_periodic_table()["zn"] == 30
+    assert isinstance(tomofusion.device_count(), list)
+    assert tomofusion.determine_gpu_config is ttv.determine_gpu_config
+    # the modules are callable like the classes they hold (both spellings are seen in user scripts)
+    assert callable(tomoengine) and callable(multigpuengine)

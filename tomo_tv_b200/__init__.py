@@ -6,6 +6,7 @@ Public surface (mirrors the reference, /root/reference/tomofusion):
     ChemicalTomo                 tomofusion.chemistry.reconstructor.ChemicalTomo
     multimodal                   tomofusion.chemistry.utils.multimodal (pybind11 class)
     multigpuengine               tomofusion.gpu.utils.multigpuengine (one rank per GPU under torchrun)
+    multigpufusion               tomofusion.chemistry.utils.multigpufusion (likewise)
     pytvlib.initialize_algorithm / run / wbp_filters / sart_orders
     determine_gpu_config, device_count      tomofusion/__init__.py
 
@@ -15,7 +16,7 @@ is the only compute path: there is no CPU fallback and no ASTRA dependency.
 from .engine import tomoengine, device_count, NativeError  # noqa: F401
 from . import pytvlib  # noqa: F401
 from .reconstructor import TomoGPU  # noqa: F401
-from .fusion import multimodal  # noqa: F401
+from .fusion import multimodal, multigpufusion  # noqa: F401
 from .chemistry import ChemicalTomo  # noqa: F401
 from .sharded import multigpuengine  # noqa: F401
 

@@ -80,12 +80,26 @@ class ChemicalTomo:
         chemTiltAngles = np.asarray(chemTiltAngles, dtype=np.float64)
         self.NprojHAADF = haadfTiltAngles.shape[0]
         self.NprojCHEM = chemTiltAngles.shape[0]
-        # one engine drives one GPU (the reference's multigpufusion fans slices out with OpenMP; the
-        # sharded path here is one process per GPU with slab engines)
-        self.tomo = multimodal(self.nx, self.ny, self.nz, np.deg2rad(haadfTiltAngles), np.deg2rad(chemTiltAngles),
-                               device=gpu_id if gpu_id >= 0 else -1)
-        if gpu_id >= 0:
-            self.tomo.set_gpu(gpu_id)
+        # One engine drives one GPU.  The reference's 'multigpu' configuration (reconstructor.py:53-63: multigpufusion fans
+        # slices out over the GPUs with OpenMP) is one process per GPU here: under torchrun every rank builds the same
+        # ChemicalTomo on the full tilt series and owns a contiguous x-slab (fusion.multigpufusion); get_recon() returns the
+        # whole 4-D volume on every rank.
+        self._dist = None
+        if gpu_id < 0:
+            try:
+                import torch.distributed as td
+                if td.is_available() and td.is_initialized() and td.get_world_size() > 1:
+                    self._dist = td
+            except ImportError:
+                pass
+        if self._dist is not None:
+            from .fusion import multigpufusion
+            self.tomo = multigpufusion(self.nx, self.ny, self.nz, np.deg2rad(haadfTiltAngles), np.deg2rad(chemTiltAngles), dist=self._dist)
+        else:
+            self.tomo = multimodal(self.nx, self.ny, self.nz, np.deg2rad(haadfTiltAngles), np.deg2rad(chemTiltAngles),
+                                   device=gpu_id if gpu_id >= 0 else -1)
+            if gpu_id >= 0:
+                self.tomo.set_gpu(gpu_id)
 
         self.set_haadf_projections(haadf)
         self.set_chemical_projections(chem)
@@ -108,7 +122,7 @@ class ChemicalTomo:
         haadf[haadf < 0] = 0
         haadf /= np.max(haadf)
         bh = np.ascontiguousarray(np.transpose(haadf, (0, 2, 1)).reshape(self.nx, self.ny * self.NprojHAADF), dtype=np.float32)
-        self.tomo.set_haadf_tilt_series(bh)
+        self.tomo.set_haadf_tilt_series(self._slab(bh))
 
     def set_chemical_projections(self, chem):
         """reconstructor.py:111-137: bChem[s] = concat_e chem[e][s].T.flatten()."""
@@ -117,7 +131,14 @@ class ChemicalTomo:
             chem[element] /= np.max(chem[element])
         parts = [np.transpose(chem[el], (0, 2, 1)).reshape(self.nx, self.ny * self.NprojCHEM) for el in self.elements]
         bChem = np.ascontiguousarray(np.concatenate(parts, axis=1), dtype=np.float32)
-        self.tomo.set_chem_tilt_series(bChem)
+        self.tomo.set_chem_tilt_series(self._slab(bChem))
+
+    def _slab(self, rows):
+        """This rank's rows of a [Nslice, ...] host array (the whole array on one GPU)."""
+        if self._dist is None:
+            return rows
+        from .sharded import slab_of
+        return slab_of(rows, self._dist)
 
     def set_summation_matrix(self, gamma: float = 1.6, sigmaMethod: int = 3):
         """reconstructor.py:139-153."""
@@ -165,7 +186,11 @@ class ChemicalTomo:
         if self.reconTotal is None:
             self.reconTotal = np.zeros([self.nz, self.nx, self.ny, self.ny], dtype=np.float32)
         for e in range(self.nz):
-            self.reconTotal[e] = self.tomo.get_recon_all(e)
+            rec = self.tomo.get_recon_all(e)
+            if self._dist is not None:
+                from .sharded import gather_slabs
+                rec = gather_slabs(rec, self._dist)
+            self.reconTotal[e] = rec
         return self.reconTotal
 
     @staticmethod

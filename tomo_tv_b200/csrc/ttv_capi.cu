@@ -327,6 +327,7 @@ int ttv_set_option(ttv_handle h, const char* name, int value) {
     const std::string nm = name ? name : "";
     if (nm == "fgp_tiled") e.fgp_tiled = value != 0;
     else if (nm == "fgp_fuse") e.fgp_fuse = value != 0;
+    else if (nm == "sart_cluster") e.sart_cluster = value != 0;
     else if (nm == "fp_variant") {
         if (value < 0 || value > 2) throw CudaError("ttv_set_option: fp_variant must be 0 (by slab thickness), 1 (classic) or 2 (table-driven)");
         e.fp_variant = value;

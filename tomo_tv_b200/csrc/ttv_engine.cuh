@@ -133,6 +133,44 @@ __global__ void __launch_bounds__(256) push_slice_kernel(const float* __restrict
     }
 }
 
+// Two-slice-deep ghosts for the two-sweeps-per-launch TV-FGP kernel (ttv_fgp2.cuh) of a sharded volume, one thread per (j,k)
+// cell: (P1, P2, P3, in) of my slices 0 and 1 -> the LEFT neighbour's ghost arrays R1, R2; of my last slice -> the RIGHT
+// neighbour's L1; P1 of my last-but-one slice -> its L2.  Full 16-byte cells, consecutive threads -> consecutive cells: the
+// peer stores are coalesced 512-byte runs over NVLink.  The last block publishes `epoch` on both neighbours (release).
+struct PushGhost {
+    const float* in; const float* P1; const float* P2; const float* P3;     // P == nullptr: first pair of a call (P = 0)
+    float4* dR1; float4* dR2; float4* dL1; float4* dL2;                      // on the left / right neighbour
+    int nx; int64_t M;
+    unsigned* cnt; unsigned* flagOnLeft; unsigned* flagOnRight; unsigned epoch;
+};
+__global__ void __launch_bounds__(256) push_ghost_kernel(const PushGhost g)
+{
+    const int xl = g.nx - 1, xm = g.nx - 2;
+    const int64_t bl = (int64_t)(xl >> 5) * g.M, bm = (int64_t)(xm >> 5) * g.M;
+    const int el = xl & 31, em = xm & 31;
+    for (int64_t m = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; m < g.M; m += (int64_t)gridDim.x * blockDim.x) {
+        const float2 i01 = *reinterpret_cast<const float2*>(g.in + m * 32);
+        float2 a = make_float2(0.f, 0.f), b = a, c = a;
+        float l1 = 0.f, l2 = 0.f, l3 = 0.f, m1 = 0.f;
+        if (g.P1) {
+            a = *reinterpret_cast<const float2*>(g.P1 + m * 32); b = *reinterpret_cast<const float2*>(g.P2 + m * 32); c = *reinterpret_cast<const float2*>(g.P3 + m * 32);
+            l1 = g.P1[(bl + m) * 32 + el]; l2 = g.P2[(bl + m) * 32 + el]; l3 = g.P3[(bl + m) * 32 + el];
+            m1 = g.P1[(bm + m) * 32 + em];
+        }
+        g.dR1[m] = make_float4(a.x, b.x, c.x, i01.x);
+        g.dR2[m] = make_float4(a.y, b.y, c.y, i01.y);
+        g.dL1[m] = make_float4(l1, l2, l3, g.in[(bl + m) * 32 + el]);
+        g.dL2[m] = make_float4(m1, 0.f, 0.f, 0.f);
+    }
+    __threadfence_system();
+    __syncthreads();
+    if (threadIdx.x == 0 && atomicAdd(g.cnt, 1u) == gridDim.x - 1) {
+        *g.cnt = 0; __threadfence_system();
+        asm volatile("st.release.sys.global.u32 [%0], %1;" ::"l"(g.flagOnLeft), "r"(g.epoch) : "memory");
+        asm volatile("st.release.sys.global.u32 [%0], %1;" ::"l"(g.flagOnRight), "r"(g.epoch) : "memory");
+    }
+}
+
 // ------------------------------------------------------------------------------------------
 // NCCL through dlopen (only touched when ttv_comm_init is called)
 // ------------------------------------------------------------------------------------------
@@ -273,7 +311,10 @@ public:
     bool p2p_ready = false; unsigned fgp_epoch = 0; int p2p_pitch = 0;
     int* d_err = nullptr;
     size_t p2p_plane_elems() const { return (size_t)N * p2p_pitch; }
-    size_t p2p_bytes() const { return 256 + (8 * p2p_plane_elems() + 2 * (size_t)N * N * 4) * sizeof(float); }
+    size_t p2p_bytes() const { return 256 + (8 * p2p_plane_elems() + 2 * (size_t)N * N * 4 + 8 * (size_t)N * N * 4) * sizeof(float); }
+    // ghost cells of the two-sweep kernel: arr 0,1 = R1,R2 (from the right neighbour), 2,3 = L1,L2 (from the left), double-buffered
+    static float* p2p_g2(float* base, size_t pe, size_t M, int arr, int parity) { return base + 64 + 8 * pe + 2 * M * 4 + (size_t)(arr * 2 + parity) * M * 4; }
+    unsigned g2_epoch = 0;
     // ghost-cell array [N][N][4] holding slice 0 of `in` of the right (ring) neighbour, double-buffered
     static float* p2p_grin(float* base, size_t pe, size_t M, int parity) { return base + 64 + 8 * pe + (size_t)parity * M * 4; }
     unsigned in_epoch = 0;
@@ -370,6 +411,7 @@ public:
         for (DBuf* d : {&recon, &yk, &recon_old, &temp, &original, &b, &g, &r, &scratch, &R, &C, &stage, &planes}) d->release();
         for (auto& d : P) d.release();
         cudaFree(d_win0); cudaFree(d_fpang); cudaFree(d_fpgrp); cudaFree(d_theta); cudaFree(d_red); cudaFree(d_imax); cudaFree(d_bpconst);
+        cudaFree(d_sartc);
         { ConstOwner& o = const_owner(device); if (o.e == this) { cudaStreamSynchronize(st); o = ConstOwner(); } }
         if (h_red) cudaFreeHost(h_red);
         if (ev_red) cudaEventDestroy(ev_red);
@@ -909,7 +951,7 @@ public:
         }
         return best;
     }
-    void fgp2_launch(int ma, int mb, const FgpParams& p, float* out) {
+    void fgp2_launch(int ma, int mb, const FgpParams& p, float* out, const float* const* ghosts = nullptr) {
         F2Maps tm;
         tm.in = make_tmap(p.in, N, N, nxb, F2_CW, 2);
         tm.inh = make_tmap(p.in, N, N, nxb, F2_CW, 2, 4);
@@ -918,6 +960,11 @@ public:
             tm.p1 = make_tmap(p.P1, N, N, nxb, F2_CW, 2); tm.p1h = make_tmap(p.P1, N, N, nxb, F2_CW, 2, 4);
             tm.p2 = make_tmap(p.P2, N, N, nxb, F2_CW, 2); tm.p2h = make_tmap(p.P2, N, N, nxb, F2_CW, 2, 4);
             tm.p3 = make_tmap(p.P3, N, N, nxb, F2_CW, 2); tm.p3h = make_tmap(p.P3, N, N, nxb, F2_CW, 2, 4);
+        }
+        tm.gR1 = tm.gR2 = tm.gL1 = tm.gL2 = tm.inh;                       // placeholders on a single volume
+        if (ghosts) {
+            tm.gR1 = make_ghost_tmap(ghosts[0], N, F2_CW, 2); tm.gR2 = make_ghost_tmap(ghosts[1], N, F2_CW, 2);
+            tm.gL1 = make_ghost_tmap(ghosts[2], N, F2_CW, 2); tm.gL2 = make_ghost_tmap(ghosts[3], N, F2_CW, 2);
         }
         const int seg = fgp2_seg();
         dim3 grid(nxb, (N + F2_TKO - 1) / F2_TKO, (N + seg - 1) / seg);
@@ -944,7 +991,29 @@ public:
         const float* hn = nullptr;
         const bool p2p = nranks > 1 && p2p_ready && fgp_tiled;
         const size_t pe = p2p ? p2p_plane_elems() : 0;
-        if (p2p) {
+        // sharded volume, two sweeps per launch: two-slice-deep ghost cells pushed into the neighbours' memory before every pair
+        // (even sweep counts; every slab at least two slices thick)
+        const bool g2 = p2p && fgp_fuse && iter >= 2 && (iter % 2 == 0) && nx >= 2 && nxg >= 2 * nranks;
+        const float* gh[4] = {nullptr, nullptr, nullptr, nullptr};
+        auto push_ghosts = [&](const float* q1, const float* q2, const float* q3) {
+            ProfScope ps(*this, PF_HALO);
+            ++g2_epoch;
+            const int par = (int)(g2_epoch & 1u);
+            const size_t M = (size_t)N * N;
+            PushGhost g;
+            g.in = recon.p; g.P1 = q1; g.P2 = q2; g.P3 = q3; g.nx = nx; g.M = (int64_t)M;
+            g.dR1 = reinterpret_cast<float4*>(p2p_g2(p2p_left, pe, M, 0, par)); g.dR2 = reinterpret_cast<float4*>(p2p_g2(p2p_left, pe, M, 1, par));
+            g.dL1 = reinterpret_cast<float4*>(p2p_g2(p2p_right, pe, M, 2, par)); g.dL2 = reinterpret_cast<float4*>(p2p_g2(p2p_right, pe, M, 3, par));
+            g.cnt = p2p_flag(p2p_base, 8); g.flagOnLeft = p2p_flag(p2p_left, 7); g.flagOnRight = p2p_flag(p2p_right, 6); g.epoch = g2_epoch;
+            push_ghost_kernel<<<(unsigned)std::min<size_t>((M + 255) / 256, 592), 256, 0, st>>>(g);
+            wait_flags_kernel<<<1, 1, 0, st>>>(p2p_flag(p2p_base, 6), p2p_flag(p2p_base, 7), g2_epoch, d_err);
+            launches += 2;
+            for (int a = 0; a < 4; ++a) gh[a] = p2p_g2(p2p_base, pe, M, a, par);
+        };
+        if (g2) {
+            push_ghosts(nullptr, nullptr, nullptr);
+            hn = gh[0] + 3;                                  // `in` of the ring neighbour's slice 0: element 3 of the R1 cells
+        } else if (p2p) {
             // peer memory: my slice 0 goes straight into the left ring neighbour's ghost cells, then wait for mine
             ProfScope ps(*this, PF_HALO);
             ++in_epoch;
@@ -972,7 +1041,7 @@ public:
         const bool has_left = nranks > 1 && rank > 0, has_right = nranks > 1 && rank < nranks - 1;
         if (has_right) p.hr_in = hn;
         int cur = 0;   // P[cur*3 ..] holds the current dual variable
-        const bool fuse = fgp_fuse && fgp_tiled && nranks == 1 && iter >= 2;
+        const bool fuse = fgp_fuse && fgp_tiled && iter >= 2 && (nranks == 1 || g2);
         for (int it = 0; it < iter; ++it) {
             const bool first = (it == 0), last = (it == iter - 1);
             if (fuse && it + 1 < iter) {
@@ -982,11 +1051,16 @@ public:
                 else { p.P1 = p.P2 = p.P3 = nullptr; }
                 const int nxt = first ? 0 : 1 - cur;
                 p.Q1 = P[nxt * 3 + 0].p; p.Q2 = P[nxt * 3 + 1].p; p.Q3 = P[nxt * 3 + 2].p;
+                if (g2) {                                    // the kernel only tests these two for "a neighbouring rank exists"
+                    p.hr_in = has_right ? gh[0] : nullptr;
+                    p.hl_P1 = has_left ? gh[2] : nullptr;
+                }
                 {
                     ProfScope ps(*this, first ? PF_FGP2_FIRST : last2 ? PF_FGP2_FINAL : PF_FGP2_SWEEP);
-                    fgp2_launch(first ? FGP_FIRST : FGP_SWEEP, last2 ? FGP_FINAL : FGP_SWEEP, p, scratch.p);
+                    fgp2_launch(first ? FGP_FIRST : FGP_SWEEP, last2 ? FGP_FINAL : FGP_SWEEP, p, scratch.p, g2 ? gh : nullptr);
                 }
                 TTV_LAUNCH_CHECK();
+                if (g2 && !last2) push_ghosts(p.Q1, p.Q2, p.Q3);
                 if (!last2) cur = nxt;
                 ++it;
                 continue;
@@ -1147,6 +1221,8 @@ public:
     // SART (A/cuda/2d/sart.cu:175-227): implemented in ttv_sart.cuh
     // ---------------------------------------------------------------------------------------
     void sart_pass(float beta, int niter);
+    bool sart_cluster = true;                       // ttv_set_option "sart_cluster": 1 = slice-resident cluster kernel (ttv_sartc.cuh) when the slice fits
+    struct SartcAngle* d_sartc = nullptr; size_t sartc_cap = 0;
 };
 
 }  // namespace ttv

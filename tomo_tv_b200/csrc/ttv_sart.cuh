@@ -91,6 +91,10 @@ __global__ void __launch_bounds__(256) sart_bp1_kernel(const SartBpParams p)
     *reinterpret_cast<float4*>(o) = x;
 }
 
+}  // namespace ttv
+#include "ttv_sartc.cuh"
+namespace ttv {
+
 inline void Engine::sart_pass(float beta, int niter) {
     need_angles();
     if (!sart_ready) throw CudaError("SART called before initialize_SART");
@@ -100,6 +104,54 @@ inline void Engine::sart_pass(float beta, int niter) {
     for (int i = 0; i < Na; ++i) sart_order[i] = i;
     if (projOrder == "random") {
         for (int i = 0; i < Na - 1; ++i) { const int k = rand() % (Na - i); std::swap(sart_order[i], sart_order[i + k]); }
+    }
+    // slice-resident cluster kernel (ttv_sartc.cuh): the whole pass in one launch when a slice fits in a cluster's shared memory
+    if (sart_cluster && niter > 0) {
+        int optin = 0;
+        TTV_CUDA(cudaDeviceGetAttribute(&optin, cudaDevAttrMaxSharedMemoryPerBlockOptin, device));
+        SartcParams q;
+        size_t smem = 0;
+        const int S = sartc_pick_S(N, nx, (size_t)optin, q.NCH, q.CR, smem);
+        if (S > 0) {
+            const int nsub = Na * niter;
+            std::vector<SartcAngle> ha(nsub);
+            for (int it = 0; it < nsub; ++it) {
+                const int a = sart_order[it % Na];
+                ha[it] = SartcAngle{geom[a].theta, geom[a].detsize, geom[a].offset, geom[a].sc, geom[a].ss, geom[a].off, geom[a].vertical, a};
+            }
+            if (sartc_cap < (size_t)nsub) {
+                cudaFree(d_sartc);
+                TTV_CUDA(cudaMalloc(&d_sartc, nsub * sizeof(SartcAngle)));
+                sartc_cap = nsub;
+            }
+            TTV_CUDA(cudaMemcpyAsync(d_sartc, ha.data(), nsub * sizeof(SartcAngle), cudaMemcpyHostToDevice, st));
+            q.vol = recon.p; q.b = b.p; q.R = R.p; q.ang = d_sartc; q.nsub = nsub; q.N = N; q.Na = Na; q.nx = nx; q.relax = sart_relax;
+            q.RB = (N + SARTC_CL - 1) / SARTC_CL;
+            cudaLaunchConfig_t cfg = {};
+            cfg.gridDim = dim3((unsigned)(SARTC_CL * ((nx + S - 1) / S)));
+            cfg.blockDim = dim3(SARTC_THREADS);
+            cfg.dynamicSmemBytes = smem;
+            cfg.stream = st;
+            cudaLaunchAttribute at[1];
+            at[0].id = cudaLaunchAttributeClusterDimension;
+            at[0].val.clusterDim.x = SARTC_CL; at[0].val.clusterDim.y = 1; at[0].val.clusterDim.z = 1;
+            cfg.attrs = at; cfg.numAttrs = 1;
+            ProfScope ps(*this, PF_SART_FP);
+            if (S == 4) {
+                TTV_CUDA(cudaFuncSetAttribute(sartc_kernel<4>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+                TTV_CUDA(cudaLaunchKernelEx(&cfg, sartc_kernel<4>, q));
+            } else if (S == 2) {
+                TTV_CUDA(cudaFuncSetAttribute(sartc_kernel<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+                TTV_CUDA(cudaLaunchKernelEx(&cfg, sartc_kernel<2>, q));
+            } else {
+                TTV_CUDA(cudaFuncSetAttribute(sartc_kernel<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+                TTV_CUDA(cudaLaunchKernelEx(&cfg, sartc_kernel<1>, q));
+            }
+            ++launches;
+            TTV_LAUNCH_CHECK();
+            sync();                                             // the host copy of the angle table is reused by the next call
+            return;
+        }
     }
     if (scratch.n < (size_t)nxb * N * 32) scratch.alloc(vol_elems());
     float* proj = scratch.p;

@@ -208,3 +208,56 @@ class multimodal:
 
     def timer_stop(self):
         v = C.c_float(0); check(lib().ttv_mm_timer_stop(self._h, C.byref(v))); return v.value
+
+
+class multigpufusion(multimodal):
+    """multigpufusion(Ns, Nray, Nel, haadfAngles, chemAngles) -- chemistry/utils/multigpufusion.hpp:21-54, binding
+    multigpufusion.cpp:459-475.
+
+    The reference fans the slices of ONE process out over the visible GPUs with OpenMP.  Here it is one process per
+    GPU: under `torchrun --nproc-per-node G` (an initialised torch.distributed group) every rank constructs this with
+    the GLOBAL Ns and gets the fusion engine of its own contiguous x-slab on GPU LOCAL_RANK (data methods then take /
+    return the rank's slab, see tomo_tv_b200.sharded.slab_of / gather_slabs); cost values, data distances and the 4-D
+    TV norms are all-reduced inside the engine (NCCL), so every rank sees the whole-volume numbers.  Without a process
+    group it is a single-GPU `multimodal`.
+    """
+
+    def __init__(self, Ns, Nray, Nelements, haadfAngles, chemAngles, dist=None):
+        import os
+        from .sharded import world
+        from .phantom import slab_bounds
+        if dist is None:
+            try:
+                import torch.distributed as td
+                dist = td if td.is_available() and td.is_initialized() else None
+            except Exception:
+                dist = None
+        rank, ws = world(dist)
+        self.global_nslice, self.rank, self.world_size, self._dist = int(Ns), rank, ws, dist
+        x0, cnt = slab_bounds(int(Ns), ws, rank)
+        self.x_offset = x0
+        local = int(os.environ.get("LOCAL_RANK", "0")) if ws > 1 else -1
+        super().__init__(cnt, Nray, Nelements, haadfAngles, chemAngles, device=local, x_offset=x0, nslice_global=int(Ns))
+        if ws > 1:
+            from .engine import tomoengine
+            uid = [tomoengine.nccl_unique_id() if rank == 0 else None]
+            dist.broadcast_object_list(uid, src=0)
+            self.comm_init(uid[0], rank, ws)
+
+    def comm_init(self, uid128, rank, nranks):
+        buf = (C.c_char * 128).from_buffer_copy(bytes(uid128))
+        check(lib().ttv_mm_comm_init(self._h, buf, int(rank), int(nranks)))
+
+    def get_gpu_ids(self):
+        import os
+        if self.world_size == 1:
+            return [max(self.get_gpu_id(), 0)]
+        ids = [None] * self.world_size
+        self._dist.all_gather_object(ids, int(os.environ.get("LOCAL_RANK", "0")))
+        return ids
+
+    def is_multi_gpu_enabled(self):
+        return self.world_size > 1
+
+    def print_gpu_usage(self):
+        print(f"rank {self.rank}/{self.world_size}: slices [{self.x_offset}, {self.x_offset + self.Nslice}) of {self.global_nslice}")
