@@ -131,7 +131,7 @@ def test_fgp_tiled_kernel_matches_oracle_and_first_generation(ttv, orc, nx, n, i
     assert S.rel_l2(outs[0][1], o.recon) <= 1e-6
 
 
-@pytest.mark.parametrize("nx,n,it,nr", [(70, 96, 4, 2), (64, 45, 3, 2), (40, 130, 5, 2), (35, 40, 10, 2), (66, 70, 6, 3), (100, 61, 4, 3), (7, 33, 8, 3)])
+@pytest.mark.parametrize("nx,n,it,nr", [(70, 96, 4, 2), (64, 45, 3, 2), (40, 130, 5, 2), (35, 40, 10, 2), (66, 70, 6, 3), (100, 61, 4, 3), (7, 33, 8, 3), (99, 50, 6, 3), (66, 40, 2, 2)])
 def test_fgp_peer_memory_handoff_two_slabs_one_gpu(ttv, nx, n, it, nr):
     """The sharded TV-FGP path without NCCL: two or three slab engines in this process, attached to each other's
     ghost buffers (plain pointers instead of CUDA IPC handles), driven by one host thread each.  Odd sweep counts run one
@@ -373,7 +373,7 @@ def test_sart_cluster_kernel_matches_per_angle_kernels(ttv, orc, nx, n, na, orde
     ang = np.deg2rad(np.sort(rng.uniform(-88, 88, na))).astype(np.float32)
     b = rng.random((nx, na * n), dtype=np.float32) * 3
     outs = []
-    for cl in (1, 0):
+    for cl in (2, 0):                                # 2: cluster kernel also where only one slice fits per cluster (N > ~360)
         eng = ttv.tomoengine(nx, n, ang)
         eng.set_option("sart_cluster", cl)
         eng.set_tilt_series(b)
@@ -385,10 +385,27 @@ def test_sart_cluster_kernel_matches_per_angle_kernels(ttv, orc, nx, n, na, orde
         l0 = eng.launch_count()
         eng.SART(0.7, 2)
         outs.append((eng.get_recon_all(), eng.launch_count() - l0))
-    assert outs[0][1] == 1 and outs[1][1] == 4 * na           # one cluster launch against 2 launches per sub-iteration
+    assert outs[0][1] < 4 and outs[1][1] >= 4 * na            # one cluster launch per pass against 2 launches per sub-iteration
     assert S.rel_l2(outs[0][0], outs[1][0]) <= 2e-6
     if order == "sequential":
         o = _oracle_for(orc, eng, nx, n, ang)
         o.set_tilt_series(b); o.initialize_SART("sequential"); o.restart_recon()
         o.SART(0.7, 2)
         assert S.rel_l2(outs[0][0], o.recon) <= 5e-6
+
+
+@pytest.mark.parametrize("nx,n", [(1, 5), (33, 63), (70, 100), (64, 129), (3, 32), (40, 31)])
+def test_tvgd_marching_kernel_is_bit_identical(ttv, nx, n):
+    """tvgd_gradient_march_kernel (three rows x three columns carried in registers along k) against the first-generation
+    tvgd_gradient_kernel: same expressions per voxel, including the reference's index quirks (tv_gd.cu:73,76,79)."""
+    rng = np.random.default_rng(nx * 7 + n)
+    v = (0.5 + 0.3 * rng.standard_normal((nx, n, n))).astype(np.float32)
+    outs = []
+    for march in (1, 0):
+        eng = ttv.tomoengine(nx, n, np.zeros(2, np.float32))
+        eng.set_option("tvgd_march", march)
+        eng.set_recon_all(v)
+        tv0 = eng.tv_gd(4, 0.3)
+        outs.append((tv0, eng.get_recon_all()))
+    assert outs[0][0] == outs[1][0]
+    assert np.array_equal(outs[0][1], outs[1][1])

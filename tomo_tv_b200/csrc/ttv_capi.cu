@@ -327,7 +327,8 @@ int ttv_set_option(ttv_handle h, const char* name, int value) {
     const std::string nm = name ? name : "";
     if (nm == "fgp_tiled") e.fgp_tiled = value != 0;
     else if (nm == "fgp_fuse") e.fgp_fuse = value != 0;
-    else if (nm == "sart_cluster") e.sart_cluster = value != 0;
+    else if (nm == "sart_cluster") { e.sart_cluster = value != 0; e.sart_cluster_force = value == 2; }
+    else if (nm == "tvgd_march") e.tvgd_march = value != 0;
     else if (nm == "fp_variant") {
         if (value < 0 || value > 2) throw CudaError("ttv_set_option: fp_variant must be 0 (by slab thickness), 1 (classic) or 2 (table-driven)");
         e.fp_variant = value;
@@ -403,6 +404,7 @@ int ttv_time_kernel(ttv_handle h, const char* name, int reps, int arg_i, float a
         else if (nm == "tv") { tv_value_tiled_kernel<<<dim3(gsw.x, (e.N + 7) / 8, e.nxb), 256, 0, e.st>>>(e.recon.p, e.dims(), nullptr, 1, e.d_red); ++e.launches; }
         else if (nm == "momentum") { momentum_kernel<<<ew_blocks(n / 4), 256, 0, e.st>>>(reinterpret_cast<float4*>(e.scratch.p), reinterpret_cast<float4*>(e.yk.p), reinterpret_cast<float4*>(e.recon_old.p), 0.5f, n / 4); ++e.launches; }
         else if (nm == "tvgd_grad") { tvgd_gradient_kernel<<<dim3(gsw.x, (e.N + 7) / 8, e.nxb), 256, 0, e.st>>>(gp); ++e.launches; }
+        else if (nm == "tvgd_grad2") { tvgd_gradient_march_kernel<<<dim3(gsw.x, (e.N + 7) / 8, e.nxb), 256, 0, e.st>>>(gp); ++e.launches; }
         else if (nm == "tvgd_update") { tvgd_update_kernel<<<ew_blocks(n / 4), 256, 0, e.st>>>(e.yk.p, e.scratch.p, e.d_red + 1, 0.f, 0, n / 4); ++e.launches; }
         else if (nm == "sqdist") { reduce_kernel<RED_SQDIST><<<ew_blocks(n / 4), 256, 0, e.st>>>(reinterpret_cast<const float4*>(e.recon.p), reinterpret_cast<const float4*>(e.yk.p), n / 4, e.d_red + 2); ++e.launches; }
         else throw CudaError("ttv_time_kernel: unknown kernel name '" + nm + "'");

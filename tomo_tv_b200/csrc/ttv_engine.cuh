@@ -1174,7 +1174,8 @@ public:
             zero_red(1);
             {
                 ProfScope ps(*this, PF_TVGD_GRAD);
-                tvgd_gradient_kernel<<<grid, 256, 0, st>>>(p); ++launches;
+                if (tvgd_march) tvgd_gradient_march_kernel<<<grid, 256, 0, st>>>(p); else tvgd_gradient_kernel<<<grid, 256, 0, st>>>(p);
+                ++launches;
             }
             TTV_LAUNCH_CHECK();
             if (nranks > 1) {
@@ -1221,6 +1222,8 @@ public:
     // SART (A/cuda/2d/sart.cu:175-227): implemented in ttv_sart.cuh
     // ---------------------------------------------------------------------------------------
     void sart_pass(float beta, int niter);
+    bool tvgd_march = true;                         // "tvgd_march": 1 = register-marching TV-GD gradient kernel, 0 = first-generation kernel
+    bool sart_cluster_force = false;                // "sart_cluster" = 2: also with one slice per cluster (slower than the per-angle kernels)
     bool sart_cluster = true;                       // ttv_set_option "sart_cluster": 1 = slice-resident cluster kernel (ttv_sartc.cuh) when the slice fits
     struct SartcAngle* d_sartc = nullptr; size_t sartc_cap = 0;
 };

@@ -112,7 +112,10 @@ inline void Engine::sart_pass(float beta, int niter) {
         SartcParams q;
         size_t smem = 0;
         const int S = sartc_pick_S(N, nx, (size_t)optin, q.NCH, q.CR, smem);
-        if (S > 0) {
+        // S = 1 (one slice per cluster, N > ~360) pays the index arithmetic of every sample for a single slice: measured 128 ms per
+        // pass at 512^3 x 180 against 113 ms for the per-angle kernels below, which share it between the 4 slices of a float4 lane --
+        // the cluster kernel is used where it keeps at least two slices per cluster (4.0 against 11.5 ms at 256^3 x 71)
+        if (S >= 2 || (S == 1 && sart_cluster_force)) {
             const int nsub = Na * niter;
             std::vector<SartcAngle> ha(nsub);
             for (int it = 0; it < nsub; ++it) {
@@ -161,10 +164,10 @@ inline void Engine::sart_pass(float beta, int niter) {
         Sart1Params f; f.vol = recon.p; f.b = b.p; f.R = R.p; f.proj = proj;
         f.theta = geom[a].theta; f.detsize = geom[a].detsize; f.offset = geom[a].offset; f.vertical = geom[a].vertical;
         f.a = a; f.N = N; f.Nd = N; f.Na = Na;
-        sart_fp1_kernel<<<gfp, 256, 0, st>>>(f); ++launches;
+        { ProfScope ps(*this, PF_SART_FP); sart_fp1_kernel<<<gfp, 256, 0, st>>>(f); ++launches; }
         SartBpParams q; q.vol = recon.p; q.proj = proj; q.sc = geom[a].sc; q.ss = geom[a].ss; q.off = geom[a].off;
         q.relax = sart_relax; q.N = N; q.Nd = N;
-        sart_bp1_kernel<<<gbp, 256, 0, st>>>(q); ++launches;
+        { ProfScope ps(*this, PF_SART_BP); sart_bp1_kernel<<<gbp, 256, 0, st>>>(q); ++launches; }
     }
     TTV_LAUNCH_CHECK();
     sync();

@@ -42,6 +42,12 @@ struct SartcParams {
     int NCH, CR;                            // chunks of a band per ray (FP work items = N * NCH), lines per chunk
 };
 
+// cluster-wide barrier with release / acquire at CLUSTER scope (orders shared::cluster accesses).  cooperative_groups'
+// cluster.sync() adds a GPU-scope MEMBAR and an L1 invalidate (CCTL.IVALL) on either side -- microseconds per angle here.
+__device__ __forceinline__ void cluster_sync_sc() {
+    asm volatile("barrier.cluster.arrive.release.aligned;\n\tbarrier.cluster.wait.acquire.aligned;" ::: "memory");
+}
+
 template <int S> struct SVec;
 template <> struct SVec<1> { typedef float T; };
 template <> struct SVec<2> { typedef float2 T; };
@@ -118,8 +124,8 @@ __global__ void __launch_bounds__(SARTC_THREADS, 1) sartc_kernel(const SartcPara
         if (A.vertical != orient) {
             // transpose through the slice's home in HBM / L2: every CTA writes its band, then reads its band of the other orientation
             store_band(orient);
-            __threadfence();
-            cluster.sync();
+            __threadfence();                                // the other CTAs read these global stores (through L2: __ldcg) after the barrier
+            cluster_sync_sc();
             orient = A.vertical;
             load_band(orient);
             __syncthreads();
@@ -172,7 +178,7 @@ __global__ void __launch_bounds__(SARTC_THREADS, 1) sartc_kernel(const SartcPara
             }
             sv_store<S>(mypart + (size_t)item * S, acc);
         }
-        cluster.sync();                                     // every CTA's partials of this angle are visible cluster-wide
+        cluster_sync_sc();                                  // every CTA's partials of this angle are visible cluster-wide
         // ---------------- weighted residual p, summed in a fixed order through DSMEM; every CTA keeps its own copy ----------------
         {
             const float cs = corr1 * (1.0f / 256.0f);
@@ -223,7 +229,7 @@ __global__ void __launch_bounds__(SARTC_THREADS, 1) sartc_kernel(const SartcPara
     }
     store_band(orient);
     // no CTA may leave while another one could still read its partials through DSMEM
-    cluster.sync();
+    cluster_sync_sc();
 }
 
 // slices per cluster that fit (0: the slice does not fit, use the per-angle kernels of ttv_sart.cuh)

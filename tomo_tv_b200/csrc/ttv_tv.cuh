@@ -356,6 +356,27 @@ struct GdParams {
     const float* x; float* g; const float* hm; const float* hp; double* sumsq; VolDims d;
 };
 
+// One voxel of tv_gradient_3D_kernel (tv_gd.cu:83-103) with the floating-point contraction the reference's own build has
+// (read from the SASS of oracle/_ref, nvcc default -fmad=true): every sqrt argument is the left-to-right chain
+// fma(d3, d3, fma(d2, d2, fma(d1, d1, eps))), the numerator of the first term is evaluated in double (3.0 * c is a double
+// product in the source), quotients are IEEE divisions added left to right.  Written with explicit intrinsics so that every
+// kernel using it rounds identically whatever the surrounding code looks like.
+__device__ __forceinline__ float tvgd_voxel(float c, float x_ip, float l_jp, float l_kp, float x_im, float x_imjp, float x_imkp,
+                                            float l_jm, float l_jmkp, float l_km, float x_ipkm, float x_jpkm)
+{
+    const float eps = 1e-6f;
+    auto ss3 = [&](float d1, float d2, float d3) { return __fsqrt_rn(__fmaf_rn(d3, d3, __fmaf_rn(d2, d2, __fmaf_rn(d1, d1, eps)))); };
+    const float v1n = (float)(((3.0 * (double)c - (double)x_ip) - (double)l_jp) - (double)l_kp);
+    const float v1d = ss3(__fsub_rn(c, x_ip), __fsub_rn(c, l_jp), __fsub_rn(c, l_kp));
+    const float v2n = __fsub_rn(c, x_im);
+    const float v2d = ss3(__fsub_rn(x_im, c), __fsub_rn(x_im, x_imjp), __fsub_rn(x_im, x_imkp));
+    const float v3n = __fsub_rn(c, l_jm);
+    const float v3d = ss3(__fsub_rn(l_jm, l_jm), __fsub_rn(l_jm, c), __fsub_rn(l_jm, l_jmkp));      // ip_jm is (x, j-1, k) itself (tv_gd.cu:73)
+    const float v4n = __fsub_rn(c, l_km);
+    const float v4d = ss3(__fsub_rn(l_km, x_ipkm), __fsub_rn(l_km, x_jpkm), __fsub_rn(l_km, c));
+    return __fadd_rn(__fadd_rn(__fadd_rn(__fdiv_rn(v1n, v1d), __fdiv_rn(v2n, v2d)), __fdiv_rn(v3n, v3d)), __fdiv_rn(v4n, v4d));
+}
+
 __global__ void __launch_bounds__(256) tvgd_gradient_kernel(const GdParams p)
 {
     const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
@@ -408,18 +429,93 @@ __global__ void __launch_bounds__(256) tvgd_gradient_kernel(const GdParams p)
             if (k == 1) { const float t = xp(L(j, 0), j, 0); x_ipkm = t; }
             else if (j >= 1) { const float t = xp(L(jm, km), jm, km); x_ipkm = t; }
             else { x_ipkm = last_g ? 0.0f : L(N - 1, km); }     // (ip-1, ny-1, km) == own slice
-            const float v1n = (float)(3.0 * (double)c - (double)x_ip - (double)l_jp - (double)l_kp);
-            const float v1d = sqrtf(eps + (c - x_ip) * (c - x_ip) + (c - l_jp) * (c - l_jp) + (c - l_kp) * (c - l_kp));
-            const float v2n = c - x_im;
-            const float v2d = sqrtf(eps + (x_im - c) * (x_im - c) + (x_im - x_imjp) * (x_im - x_imjp) + (x_im - x_imkp) * (x_im - x_imkp));
-            const float v3n = c - l_jm;
-            const float v3d = sqrtf(eps + (l_jm - l_jm) * (l_jm - l_jm) + (l_jm - c) * (l_jm - c) + (l_jm - l_jmkp) * (l_jm - l_jmkp));
-            const float v4n = c - l_km;
-            const float v4d = sqrtf(eps + (l_km - x_ipkm) * (l_km - x_ipkm) + (l_km - x_jpkm) * (l_km - x_jpkm) + (l_km - c) * (l_km - c));
-            float g = v1n / v1d + v2n / v2d + v3n / v3d + v4n / v4d;
+            float g = tvgd_voxel(c, x_ip, l_jp, l_kp, x_im, x_imjp, x_imkp, l_jm, l_jmkp, l_km, x_ipkm, x_jpkm);
             if (!valid) g = 0.0f;
             p.g[((int64_t)xb * cpb + (int64_t)j * N + k) * 32 + lane] = g;
             tot += (double)(g * g);
+        }
+    }
+    tot = warp_sum(tot);
+    __shared__ double sh[8];
+    if (lane == 0) sh[w] = tot;
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        double s = 0;
+        for (int i = 0; i < 8; ++i) s += sh[i];
+        atomicAdd(p.sumsq, s);
+    }
+}
+
+// Same gradient, marching form: a warp walks its row segment along k and keeps the three rows (j-1, j, j+1) of the three
+// columns (k-1, k, k+1) plus their x-neighbour values in registers, so a step loads ONE new column (3 lines + the edge lanes'
+// neighbour-block / halo values) instead of re-reading 7 lines and re-shuffling 6 values per voxel.  Every voxel is evaluated
+// with exactly the expressions of tvgd_gradient_kernel (same operands, same order): the two kernels are bit-identical
+// (tests/test_gpu_parity.py), and so is the comparison with the reference at realistic sizes (tests/golden C_gd10).
+__global__ void __launch_bounds__(256) tvgd_gradient_march_kernel(const GdParams p)
+{
+    const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
+    const int N = p.d.N, nx = p.d.nx;
+    const int64_t cpb = (int64_t)N * N;
+    const int j = blockIdx.y * 8 + w;
+    const int xb = blockIdx.z;
+    const int k0 = blockIdx.x * TV_KSEG;
+    const float eps = 1e-6f;
+    const float* __restrict__ x = p.x;
+    float* __restrict__ g = p.g;
+    double tot = 0.0;
+    if (j < N) {
+        const int xl = xb * 32 + lane;
+        const bool valid = xl < nx;
+        const int xg = p.d.xoff + xl;
+        const bool first_g = (xg == 0), last_g = (xg == p.d.nxg - 1);
+        const int jp = (j + 1) % N, jm = (j - 1 + N) % N;
+        const int kend = min(k0 + TV_KSEG, N);
+        // lane 0's slice x-1 and the edge lane's slice x+1 live in another x-block, a halo plane or (periodic) this volume's far end
+        const float* lp; int64_t ls;
+        if (xb > 0) { lp = x + ((int64_t)(xb - 1)) * cpb * 32 + 31; ls = 32; }
+        else if (p.hm) { lp = p.hm; ls = 1; }
+        else { lp = x + ((int64_t)((nx - 1) >> 5)) * cpb * 32 + ((nx - 1) & 31); ls = 32; }
+        const bool redge = valid && (xl == nx - 1 || lane == 31);
+        const float* rp; int64_t rs;
+        if (xl == nx - 1) { if (p.hp) { rp = p.hp; rs = 1; } else { rp = x; rs = 32; } }
+        else { rp = x + ((int64_t)(xb + 1)) * cpb * 32; rs = 32; }
+        const float* rowA = x + ((int64_t)xb * cpb + (int64_t)j * N) * 32 + lane;
+        const float* rowB = x + ((int64_t)xb * cpb + (int64_t)jm * N) * 32 + lane;
+        const float* rowC = x + ((int64_t)xb * cpb + (int64_t)jp * N) * 32 + lane;
+        const int64_t oA = (int64_t)j * N, oB = (int64_t)jm * N, oC = (int64_t)jp * N;
+
+        // one column: the three lines and the x-neighbour values derived from them
+        struct Col { float A, B, C, xmA, xpA, xpB, xmC; };
+        auto load_col = [&](int kk) {
+            Col q;
+            q.A = rowA[(int64_t)kk * 32]; q.B = rowB[(int64_t)kk * 32]; q.C = rowC[(int64_t)kk * 32];
+            q.xmA = __shfl_up_sync(0xffffffffu, q.A, 1);
+            q.xmC = __shfl_up_sync(0xffffffffu, q.C, 1);
+            q.xpA = __shfl_down_sync(0xffffffffu, q.A, 1);
+            q.xpB = __shfl_down_sync(0xffffffffu, q.B, 1);
+            if (lane == 0) { q.xmA = lp[(oA + kk) * ls]; q.xmC = lp[(oC + kk) * ls]; }
+            if (redge) { q.xpA = rp[(oA + kk) * rs]; q.xpB = rp[(oB + kk) * rs]; }
+            return q;
+        };
+        Col cm = load_col((k0 - 1 + N) % N), cc = load_col(k0);
+#pragma unroll 2
+        for (int k = k0; k < kend; ++k) {
+            const Col cp = load_col((k + 1) % N);
+            const float c = cc.A, l_jp = cc.C, l_jm = cc.B, l_kp = cp.A, l_km = cm.A, l_jmkp = cp.B;
+            const float x_ip = cc.xpA, x_im = cc.xmA, x_imjp = cc.xmC, x_imkp = cp.xmA;
+            float x_jpkm;
+            if (k == 1) x_jpkm = cm.C;
+            else if (j < N - 1) x_jpkm = l_km;
+            else x_jpkm = first_g ? 0.0f : cm.xmA;
+            float x_ipkm;
+            if (k == 1) x_ipkm = cm.xpA;
+            else if (j >= 1) x_ipkm = cm.xpB;
+            else x_ipkm = last_g ? 0.0f : cm.B;
+            float gg = tvgd_voxel(c, x_ip, l_jp, l_kp, x_im, x_imjp, x_imkp, l_jm, l_jmkp, l_km, x_ipkm, x_jpkm);
+            if (!valid) gg = 0.0f;
+            g[((int64_t)xb * cpb + (int64_t)j * N + k) * 32 + lane] = gg;
+            tot += (double)(gg * gg);
+            cm = cc; cc = cp;
         }
     }
     tot = warp_sum(tot);
