@@ -47,3 +47,15 @@ def test_sharded_equals_whole_volume_on_all_gpus(ttv):
                        capture_output=True, text=True, timeout=600, env=env, cwd=ROOT)
     assert r.returncode == 0, (r.stdout[-3000:], r.stderr[-3000:])
     assert "MGPU_CHECK PASS" in r.stdout and "MGPU_API_CHECK PASS" in r.stdout, r.stdout[-3000:]
+
+
+@pytest.mark.skipif("_gpus() < 2", reason="needs at least two GPUs")
+def test_sharded_fusion_equals_whole_volume(ttv):
+    """multigpufusion (one slab engine per rank) against multimodal on one GPU: the data-fusion scenario of config c4."""
+    n = 2
+    env = dict(os.environ, MASTER_ADDR="127.0.0.1")
+    r = subprocess.run([sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--master-addr", "127.0.0.1", "--master-port", "29543",
+                        "--nproc-per-node", str(n), os.path.join(ROOT, "tests", "mgpu_fusion_check.py"), "G"],
+                       capture_output=True, text=True, timeout=600, env=env, cwd=ROOT)
+    assert r.returncode == 0, (r.stdout[-3000:], r.stderr[-3000:])
+    assert "MGPU_FUSION_CHECK PASS" in r.stdout, r.stdout[-3000:]
