@@ -14,12 +14,16 @@ struct Sart1Params {
     int a, N, Nd, Na;
 };
 
-// block = 8 warps; warp = 4 rays x 8 float4 lanes
+// block = 8 warps; warp = ONE ray: 8 float4 lanes (32 slices) x 4 line quarters.  A quarter is a run of whole 64-line restart
+// periods of the position recurrence (par_fp.cu:49,282-286), so every sample position is the reference's; the four partial
+// sums are combined by two shuffles in a fixed order (the same for any slab thickness: sharded == whole bit for bit; it
+// differs from the reference's single running sum by rounding).  One warp per ray keeps 148 SMs busy on a 64-slice slab
+// (one ray per quarter warp left 32 CTAs there) and quadruples the loads in flight.
 __global__ void __launch_bounds__(256) sart_fp1_kernel(const Sart1Params p)
 {
     const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
-    const int lx = lane & 7, lr = lane >> 3;
-    const int d = (blockIdx.x * 8 + w) * 4 + lr;
+    const int lx = lane & 7, lq = lane >> 3;
+    const int d = blockIdx.x * 8 + w;
     const int xb = blockIdx.y;
     const int N = p.N;
     if (d >= p.Nd) return;
@@ -35,24 +39,46 @@ __global__ void __launch_bounds__(256) sart_fp1_kernel(const Sart1Params p)
     const int64_t s_line = p.vertical ? (int64_t)N * 32 : 32;
     float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
     float fP = 0.f;
-    for (int line = 0; line < N; ++line) {
-        if ((line & 63) == 0) {
-            const float t2 = __fadd_rn(__fmaf_rn((float)N, -0.5f, (float)line), 0.5f);
-            float f = __fmaf_rn(t2, step, m);
-            f = __fmaf_rn((float)N, 0.5f, f);
-            f = __fadd_rn(f, -0.5f);
-            fP = __fadd_rn(f, 0.5f);
-        } else fP = __fadd_rn(fP, step);
-        const int q = __float2int_rd(fP * 256.0f + 0.5f) - 128;   // round half up (ttv_common.cuh)
-        const int i = q >> 8;
-        const float w1 = (float)(q & 255), w0 = 256.0f - w1;
-        float4 v0 = make_float4(0.f, 0.f, 0.f, 0.f), v1 = v0;
-        const float* lp = base + line * s_line;
-        if (i >= 0 && i < N) v0 = *reinterpret_cast<const float4*>(lp + i * s_interp);
-        if (i + 1 >= 0 && i + 1 < N) v1 = *reinterpret_cast<const float4*>(lp + (i + 1) * s_interp);
-        acc.x = fmaf(w1, v1.x, fmaf(w0, v0.x, acc.x)); acc.y = fmaf(w1, v1.y, fmaf(w0, v0.y, acc.y));
-        acc.z = fmaf(w1, v1.z, fmaf(w0, v0.z, acc.z)); acc.w = fmaf(w1, v1.w, fmaf(w0, v0.w, acc.w));
+    // four lines per trip: positions first, then all eight loads in flight, then the arithmetic in line order (the sums are
+    // accumulated exactly as in a one-line loop; the kernel is bound by memory latency, not by issue slots)
+    const int chunk = ((N + 255) / 256) * 64;               // lines per quarter: a multiple of the 64-line restart period
+    const int la = lq * chunk, lb = min(N, la + chunk);
+    for (int l4 = la; l4 < lb; l4 += 4) {
+        float4 v0[4], v1[4]; float w0[4], w1[4];
+#pragma unroll
+        for (int u = 0; u < 4; ++u) {
+            const int line = l4 + u;
+            if ((line & 63) == 0) {
+                const float t2 = __fadd_rn(__fmaf_rn((float)N, -0.5f, (float)line), 0.5f);
+                float f = __fmaf_rn(t2, step, m);
+                f = __fmaf_rn((float)N, 0.5f, f);
+                f = __fadd_rn(f, -0.5f);
+                fP = __fadd_rn(f, 0.5f);
+            } else fP = __fadd_rn(fP, step);
+            const int q = __float2int_rd(fP * 256.0f + 0.5f) - 128;   // round half up (ttv_common.cuh)
+            const int i = q >> 8;
+            w1[u] = (float)(q & 255); w0[u] = 256.0f - w1[u];
+            v0[u] = make_float4(0.f, 0.f, 0.f, 0.f); v1[u] = v0[u];
+            if (line < lb) {
+                const float* lp = base + line * s_line;
+                if (i >= 0 && i < N) v0[u] = *reinterpret_cast<const float4*>(lp + i * s_interp);
+                if (i + 1 >= 0 && i + 1 < N) v1[u] = *reinterpret_cast<const float4*>(lp + (i + 1) * s_interp);
+            }
+        }
+#pragma unroll
+        for (int u = 0; u < 4; ++u) {
+            if (l4 + u < lb) {
+                acc.x = fmaf(w1[u], v1[u].x, fmaf(w0[u], v0[u].x, acc.x)); acc.y = fmaf(w1[u], v1[u].y, fmaf(w0[u], v0[u].y, acc.y));
+                acc.z = fmaf(w1[u], v1[u].z, fmaf(w0[u], v0[u].z, acc.z)); acc.w = fmaf(w1[u], v1[u].w, fmaf(w0[u], v0[u].w, acc.w));
+            }
+        }
     }
+#pragma unroll
+    for (int o = 8; o <= 16; o <<= 1) {                     // (q0 + q1) + (q2 + q3)
+        acc.x += __shfl_xor_sync(0xffffffffu, acc.x, o); acc.y += __shfl_xor_sync(0xffffffffu, acc.y, o);
+        acc.z += __shfl_xor_sync(0xffffffffu, acc.z, o); acc.w += __shfl_xor_sync(0xffffffffu, acc.w, o);
+    }
+    if (lq != 0) return;
     const float cs = corr1 * (1.0f / 256.0f);
     const float4 bb = *reinterpret_cast<const float4*>(p.b + (((size_t)xb * p.Na + p.a) * p.Nd + d) * 32 + lx * 4);
     const float wgt = p.R[(size_t)p.a * p.Nd + d];
@@ -158,7 +184,7 @@ inline void Engine::sart_pass(float beta, int niter) {
     }
     if (scratch.n < (size_t)nxb * N * 32) scratch.alloc(vol_elems());
     float* proj = scratch.p;
-    dim3 gfp((N + 31) / 32, nxb), gbp((unsigned)(((int64_t)N * N + 31) / 32), nxb);
+    dim3 gfp((N + 7) / 8, nxb), gbp((unsigned)(((int64_t)N * N + 31) / 32), nxb);
     for (int it = 0; it < Na * niter; ++it) {
         const int a = sart_order[it % Na];
         Sart1Params f; f.vol = recon.p; f.b = b.p; f.R = R.p; f.proj = proj;
