@@ -302,8 +302,9 @@ def run_ours(args):
         "fp": V + 2 * S,                                        # read x, read b, write residual (fused SIRT residual)
         "bp": S + 2 * V,                                        # read residual, read x, write x (fused SIRT update)
         "fgp_first": 4 * V, "fgp_sweep": 7 * V, "fgp_final": 5 * V, "tv": V, "momentum": 3 * V,
-        # two sweeps per launch (ttv_fgp2.cuh): the pair moves what ONE sweep of its kind moves
-        "fgp2_first": 4 * V, "fgp2_sweep": 7 * V, "fgp2_final": 5 * V,
+        # two sweeps per launch (ttv_fgp2.cuh): SURVEY 8d's per-sweep figures x the two sweeps one launch processes
+        # (FIRST 4V + SWEEP 7V, SWEEP 7V + SWEEP 7V, SWEEP 7V + FINAL 5V); the launch MOVES about half of that (see `traffic`)
+        "fgp2_first": 11 * V, "fgp2_sweep": 14 * V, "fgp2_final": 12 * V,
     }
     groups = {}
     for g, (tot, cnt) in prof.items():
@@ -328,7 +329,12 @@ def run_ours(args):
                 "bound": "hbm", "achieved": groups[dom]["achieved_gbs"], "peak": pk["hbm_gbs"], "unit": "GB/s",
                 "frac": groups[dom]["frac_of_hbm_peak"], "traffic": traffic_512().get(dom) if (n, na, world) == (512, 180, 1) else None, "peak_kind": pk_kind,
                 "algorithmic_bytes_per_launch": alg_bytes[dom], "share_of_step": groups[dom]["share_of_step"],
+                "note": ("two TV-FGP sweeps per launch: `achieved` counts the algorithmic bytes of both sweeps (2 x SURVEY 8d), so frac > 1 means the "
+                         "temporal fusion beats the per-sweep HBM roofline; `traffic` / duration is what HBM actually delivers" if dom.startswith("fgp2") else None),
                 "traffic_note": "dram__bytes_read.sum + dram__bytes_write.sum per launch from profiles/traffic_512.json (ncu --set full, 512^3 x 180, 1 GPU); null without a capture"}
+    if roof and roof.get("traffic"):
+        roof["traffic_gbs"] = roof["traffic"] / (groups[dom]["ms_per_launch"] * 1e-3) / 1e9
+        roof["traffic_frac_of_peak"] = roof["traffic_gbs"] / pk["hbm_gbs"]
     sm_mhz = (clk or {}).get("sm_mhz") or pk.get("sm_max_mhz") or 1965.0
     try:
         n_sm = torch.cuda.get_device_properties(local).multi_processor_count
