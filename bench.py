@@ -294,6 +294,17 @@ def run_ours(args):
         digests = [d for _, ds in sorted(allg, key=lambda t: t[0]) for d in ds]
     recon_sha = hashlib.sha256(b"".join(digests)).hexdigest()
     recon_tv = eng.tv()                                         # TV of the final volume (all-reduced scalar)
+    # Under momentum the reference discards the TV step (tomoengine.cpp:382: recon is overwritten by the momentum copy), so the
+    # hash above covers the projector / momentum path only.  The TV-FGP path with its ghost hand-off gets its own hash: one more
+    # tv_fgp on the final volume (outside every timed region), hashed the same way.
+    eng.tv_fgp(NTV, LAMBDA)
+    eng.get_recon_all_into(out_np)
+    digests = [hashlib.sha256(out_np[i].tobytes()).digest() for i in range(nloc)]
+    if dist is not None:
+        allg = [None] * world
+        dist.all_gather_object(allg, (x0, digests))
+        digests = [d for _, ds in sorted(allg, key=lambda t: t[0]) for d in ds]
+    fgp_sha = hashlib.sha256(b"".join(digests)).hexdigest()
 
     # ---------------- roofline of the dominant kernel ----------------
     pk, pk_kind = peaks()
@@ -368,7 +379,7 @@ def run_ours(args):
             "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": int(S / args.steps),
                     "d2h_bytes_per_step": int(V / args.steps) + 4},
             "gpu_launches": launches,
-            "recon_sha256": recon_sha, "recon_tv": recon_tv,
+            "recon_sha256": recon_sha, "recon_tv": recon_tv, "tv_fgp_sha256": fgp_sha,
             "clocks": clk,
             "roofline": roof,
             "projector_roofline": proj_roof,
