@@ -33,6 +33,22 @@ def test_c2_full_size_matches_the_reference_engine(ttv, tmp_path):
     assert d["rel_l2_vs_reference"] <= 1e-4, d
 
 
+def _have_ref_mm():
+    return bool(glob.glob(os.path.join(ROOT, "oracle", "_ref", "multimodal*.so")))
+
+
+@pytest.mark.skipif(not _have_ref_mm(), reason="oracle/_ref multimodal (compiled reference) not present")
+def test_c4_fusion_matches_the_reference_engine_at_96(ttv, tmp_path):
+    """Config c4's data-fusion scenario at 96^3 x 3 elements (71 ADF + 11 chemical angles) against the unmodified reference fusion
+    engine on identical inputs (the committed fusion goldens are 32^3 / 40^3; 256^3 is measured by the same script, profiles/)."""
+    out = tmp_path / "c4.json"
+    r = subprocess.run([sys.executable, os.path.join(ROOT, "tests", "c4_fusion_parity.py"), "--size", "96", "--out", str(out)],
+                       capture_output=True, text=True, timeout=900)
+    assert r.returncode == 0, r.stderr[-2000:]
+    d = json.load(open(out))
+    assert d["ok"], d
+
+
 def _gpus():
     import torch
     return torch.cuda.device_count()
