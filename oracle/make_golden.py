@@ -82,6 +82,17 @@ def main():
                 again = fn(r_eng, inp, nx)
                 del r_eng
                 sp = {k: np.float64(S.rel_l2(again[k], want[k])) for k in want}
+                if scn == "asd":
+                    # sensitivity of the UNMODIFIED reference to its input: the measured data moved by one ulp (random sign per
+                    # value); the change of its ASD-POCS outputs is the floor below which no two float32 implementations agree
+                    rng = np.random.default_rng(99)
+                    b1 = np.nextafter(inp["b"], np.where(rng.random(inp["b"].shape) < 0.5, -np.inf, np.inf).astype(np.float32)).astype(np.float32)
+                    r_eng = ref_mod.tomoengine(nx, n, ang)
+                    pert = fn(r_eng, dict(inp, b=b1), nx)
+                    del r_eng
+                    for k in want:
+                        sp[k + "_sens"] = np.float64(S.rel_l2(pert[k], want[k]))
+                    say(f"{geom}/{scn}: reference with inputs moved by one ulp  " + "  ".join(f"{k}={sp[k + '_sens']:.3e}" for k in sorted(want)))
                 np.savez_compressed(os.path.join(args.out, f"spread_{geom}_{scn}.npz"), **sp)
                 say(f"{geom}/{scn}: reference run-to-run spread  " + "  ".join(f"{k}={v:.3e}" for k, v in sorted(sp.items())))
                 t1 = time.time()

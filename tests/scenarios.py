@@ -266,15 +266,15 @@ TOL = {
     ("kl_bp", "recon"): 1e-5,
     # ASD-POCS alternates SART with TV-GD steps x -= dPOCS*g/|g| whose gradient terms v/sqrt(1e-6+|grad|^2) amplify
     # float32 rounding noise ~1000x wherever the volume is flat (the clamped-to-zero background).  Measured on a B200
-    # (profiles/r2_parity_table.txt): TV-GD ALONE is bit-identical to the reference at a realistic size (C/gd10 and
-    # C/tv/gd: relative L2 = 0, unmasked) and every scalar the algorithm steers by (dd, dp, tv) agrees to <= 6e-6 at C;
-    # the ASD-POCS VOLUME differs by 1.7e-3 at C although its two halves agree to 8e-7 (SART) and 0 (TV-GD).  That is
-    # the algorithm's own conditioning: two runs of the UNMODIFIED reference on the same inputs differ by 6.8e-3 (A) and
-    # 2.5e-3 (B) in `recon` (tests/golden/spread_*_asd.npz; its TV-GD kernel reads out of bounds on small grids), and the
-    # reference fed with inputs perturbed by one ulp moves by spread_C_asd.npz:recon_sens.  The volume tolerance is
-    # therefore "within the reference's own spread", the scalars keep north_star's 1e-4 at C.
-    ("asd", "recon"): 2e-2,
-    ("C", "asd", "recon"): 5e-3,
+    # (profiles/r2_parity_table.txt, r2x_asd_sensitivity.txt): TV-GD ALONE is bit-identical to the reference at a realistic size
+    # (C/gd10 and C/tv/gd: relative L2 = 0, unmasked) and every scalar the algorithm steers by (dd, dp, tv) agrees to <= 6e-6 at
+    # C; the ASD-POCS VOLUME differs by 1.2e-3 at C although its two halves agree to 8e-7 (SART) and 0 (TV-GD).  That is the
+    # algorithm's own conditioning: the UNMODIFIED reference fed with the same measured data moved by ONE ULP changes its own
+    # volume by 1.05e-3 at C (4.5e-3 at A, 7.2e-3 at B) while its scalars move by 2e-7, and two runs of it on identical inputs
+    # differ by 4e-3 (A) / 9e-3 (B) on the small grids (its TV-GD kernel reads out of bounds there).  Both numbers are stored
+    # next to the goldens (tests/golden/spread_<geom>_asd.npz: recon, recon_sens); the volume is required to agree "within the
+    # reference's own spread": 3 x max(one-ulp sensitivity, run-to-run spread) -- see tol_for().  The scalars keep north_star's
+    # 1e-4 at C.
     # small grids: the out-of-bounds reads make the reference's own ASD-POCS scalars vary from run to run
     # (spread_A_asd / spread_B_asd: 1.9e-5; an earlier generation on the same B200: 1.08e-4)
     ("A", "asd", "dp"): 5e-4, ("A", "asd", "tv"): 5e-4, ("A", "asd", "dd"): 5e-4,
@@ -313,7 +313,20 @@ GD_MASKED = {("tv", "gd"): 5, ("gd10", "gd10"): 10}      # (scenario, key) -> in
 GD_UNMASKED_GEOMS = ("C",)
 
 
+_SPREAD = {}
+
+
 def tol_for(geom, scn, k):
+    if (scn, k) == ("asd", "recon"):
+        # within the reference's own spread (measured, stored with the goldens); 2e-2 for a geometry without a stored spread
+        if geom not in _SPREAD:
+            import os
+            f = os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden", f"spread_{geom}_asd.npz")
+            _SPREAD[geom] = dict(np.load(f)) if geom is not None and os.path.exists(f) else None
+        sp = _SPREAD[geom]
+        if sp is None or "recon_sens" not in sp:
+            return 2e-2
+        return max(DEFAULT_TOL, 3.0 * max(float(sp["recon_sens"]), float(sp["recon"])))
     return TOL.get((geom, scn, k), TOL.get((scn, k), DEFAULT_TOL))
 
 
