@@ -7,8 +7,7 @@ from tomo_tv_b200.phantom import phantom3d
 
 args = [a for a in sys.argv[1:] if "=" not in a]
 n, nx, na = (int(v) for v in (args + ["512", "128", "180"][len(args):])[:3])
-runs = [a for a in sys.argv[1:] if "=" in a] or ["fp_variant=0:fp_sirt", "fp_variant=1:fp_sirt", "fp_variant=8:fp_sirt",
-                                                  "bp_variant=4:bp_sirt", "bp_variant=5:bp_sirt", "bp_variant=8:bp_sirt", "bp_variant=9:bp_sirt"]
+runs = [a for a in sys.argv[1:] if "=" in a] or ["fp_variant=1:fp_sirt", "fp_variant=2:fp_sirt", "bp_variant=1:bp_sirt", "bp_variant=2:bp_sirt"]
 ang = np.deg2rad(np.linspace(-90, 90, na, endpoint=False)).astype(np.float32)
 eng = ttv.tomoengine(nx, n, ang)
 eng.initialize_initial_volume(); eng.set_recon_all(phantom3d(nx, n))
