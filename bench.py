@@ -251,9 +251,9 @@ def run_ours(args):
 
     # ---------------- device-resident timed region ----------------
     clocks = ClockSampler(local)
-    barrier()
     if rank == 0:
-        clocks.start()
+        clocks.start()                          # before the barrier: spawning nvidia-smi on rank 0 must not skew the ranks' start
+    barrier()
     eng.profile(True)
     l0 = eng.launch_count()
     eng.timer_start()
