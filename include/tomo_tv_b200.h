@@ -198,8 +198,11 @@ int ttv_timer_stop(ttv_handle h, float* ms);
 /* implementation switches for A/B tests: "fgp_tiled" (1 = TMA-tiled TV-FGP sweep, 0 = first-generation kernel);
  * "fgp_fuse" (1 = two FGP sweeps per launch on a single-volume engine, ttv_fgp2.cuh; 0 = one launch per sweep);
  * "fp_variant" / "bp_variant" (0 = by slab thickness, 1 = classic fp_kernel / bp_kernel, 2 = table-driven fpt_kernel /
- * bpt_kernel); "bp_xb" (x-blocks per CTA of bpt_kernel: 0 = by slab thickness, 2, 8).  Every value selects a kernel the
- * GPU tests validate (all variants are bit-identical to each other). */
+ * bpt_kernel); "bp_xb" (x-blocks per CTA of bpt_kernel: 0 = by slab thickness, 2, 8); "sart_cluster" (1 = slice-resident cluster
+ * kernel of ttv_sartc.cuh where at least two slices fit in a cluster's shared memory, 2 = also with one slice per cluster, 0 = one
+ * launch pair per angle); "tvgd_march" (1 = register-marching TV-GD gradient kernel, 0 = first-generation kernel).  Every value
+ * selects a kernel the GPU tests validate (projector, TV-FGP and TV-GD variants are bit-identical to each other; the two SART
+ * paths agree to float32 rounding). */
 int ttv_set_option(ttv_handle h, const char* name, int value);
 /* self-test of the inlined 1/sqrt used by the TV-FGP projection step: number of n pseudo-random arguments > 1 whose result
  * differs from IEEE div(1, sqrt(x)) (the reference's expression, tv_fgp.cu:106); must be 0 */
