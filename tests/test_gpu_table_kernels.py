@@ -53,9 +53,9 @@ def test_fpt_matches_fp(ttv, nx, n, na):
     vol = rng.random((nx, n, n), dtype=np.float32)
     b = rng.random((nx, na * n), dtype=np.float32) * 3
     outs = []
-    for v in (1, 2):
+    for v, xb in ((1, 0), (2, 2), (2, 1)):           # classic; table-driven with 2 x-blocks per CTA; with 1 (thin slabs)
         eng = ttv.tomoengine(nx, n, ang)
-        eng.set_option("fp_variant", v); eng.set_option("bp_variant", 1)
+        eng.set_option("fp_variant", v); eng.set_option("fp_xb", xb); eng.set_option("bp_variant", 1)
         eng.initialize_initial_volume()
         eng.set_recon_all(vol); eng.forward_projection()
         g = eng.get_model_projections()
@@ -64,10 +64,11 @@ def test_fpt_matches_fp(ttv, nx, n, na):
         dd = eng.data_distance()
         eng.initialize_poisson_ML(); eng.set_recon_all(np.full((nx, n, n), 0.3, np.float32))
         outs.append((g, rec, dd, eng.poisson_ML(0.4)))
-    for a, c in zip(outs[0][:2], outs[1][:2]):
-        assert np.array_equal(a, c)
-    assert abs(outs[0][2] - outs[1][2]) <= 1e-5 * abs(outs[0][2])
-    assert abs(outs[0][3] - outs[1][3]) <= 1e-5 * abs(outs[0][3])
+    for other in outs[1:]:
+        for a, c in zip(outs[0][:2], other[:2]):
+            assert np.array_equal(a, c)
+        assert abs(outs[0][2] - other[2]) <= 1e-5 * abs(outs[0][2])
+        assert abs(outs[0][3] - other[3]) <= 1e-5 * abs(outs[0][3])
 
 
 def test_default_choice_by_slab_thickness(ttv):

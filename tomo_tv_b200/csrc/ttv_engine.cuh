@@ -284,7 +284,7 @@ public:
 
     // FP plan
     int* d_win0 = nullptr; FpAngle* d_fpang = nullptr; FpGroup* d_fpgrp = nullptr;
-    int fp_ngroups = 0, fp_ndg = 0, fp_CW = 0, fp_TR = 2, fp_S = 2; size_t fp_smem = 0; int fpt_NS = 0; size_t fpt_smem = 0;
+    int fp_ngroups = 0, fp_ndg = 0, fp_CW = 0, fp_TR = 2, fp_S = 2; size_t fp_smem = 0; int fpt_NS = 0; size_t fpt_smem = 0; int fpt1_NS = 0; size_t fpt1_smem = 0;
     float* d_theta = nullptr;
 
     // state (x-interleaved)
@@ -575,6 +575,8 @@ public:
         fpt_NS = (int)std::min<size_t>(FPT_MAX_SLOTS, (size_t)(220 * 1024) / fpt_slot_bytes(CW));
         if (fpt_NS < 3) throw CudaError("forward-projector line slot does not fit in shared memory");
         fpt_smem = (size_t)fpt_NS * fpt_slot_bytes(CW) + 2 * fpt_NS * sizeof(uint64_t);
+        fpt1_NS = (int)std::min<size_t>(FPT_MAX_SLOTS, (size_t)(220 * 1024) / fpt_slot_bytes(CW, 1));
+        fpt1_smem = (size_t)fpt1_NS * fpt_slot_bytes(CW, 1) + 2 * fpt1_NS * sizeof(uint64_t);
         fp_smem = (size_t)S * stage_b + (size_t)(S * TR + 1) * sizeof(float) + 2 * S * sizeof(uint64_t) + 16;
         cudaFree(d_win0); cudaFree(d_fpang); cudaFree(d_fpgrp); cudaFree(d_theta);
         TTV_CUDA(cudaMalloc(&d_win0, win.size() * sizeof(int)));
@@ -596,7 +598,8 @@ public:
         TTV_CUDA(cudaDeviceGetAttribute(&optin, cudaDevAttrMaxSharedMemoryPerBlockOptin, device));
         if ((size_t)optin < fp_smem) throw CudaError("forward-projector plan needs more shared memory than the device offers");
         TTV_CUDA(cudaFuncSetAttribute(fp_kernel<EPI>, cudaFuncAttributeMaxDynamicSharedMemorySize, optin));
-        TTV_CUDA(cudaFuncSetAttribute(fpt_kernel<EPI>, cudaFuncAttributeMaxDynamicSharedMemorySize, optin));
+        TTV_CUDA(cudaFuncSetAttribute(fpt_kernel<EPI, 2>, cudaFuncAttributeMaxDynamicSharedMemorySize, optin));
+        TTV_CUDA(cudaFuncSetAttribute(fpt_kernel<EPI, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize, optin));
     }
     template <int EPI> void bp_attr() {
         TTV_CUDA(cudaFuncSetAttribute(bp_kernel<EPI>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)BP_SMEM));
@@ -635,12 +638,20 @@ public:
         p.N = N; p.Nd = N; p.Na = Na; p.ndg = fp_ndg; p.CW = fp_CW; p.TR = fp_TR; p.S = fp_S;
         p.out = out; p.b = bmeas; p.R = R.p; p.red = red; p.eps = eps;
         ProfScope ps(*this, PF_FP);
-        if (fp_variant == 2 || (fp_variant == 0 && zb >= 4)) {        // below 4 x-blocks the table kernel has too few CTAs for 148 SMs
-            // table-driven kernel (ttv_fpt.cuh): 2 x-blocks per CTA, one line per slot
-            CUtensorMap tmV = make_tmap_xb(vol, N, N, zb, FPT_XB, fp_CW, 1);
-            CUtensorMap tmH = make_tmap_xb(vol, N, N, zb, FPT_XB, 1, fp_CW);
-            dim3 grid(fp_ndg, fp_ngroups, (zb + FPT_XB - 1) / FPT_XB);
-            fpt_kernel<EPI><<<grid, FPT_THREADS, fpt_smem, st>>>(tmV, tmH, p, zb, fpt_NS);
+        if (fp_variant == 2 || (fp_variant == 0 && zb >= 2)) {
+            // table-driven kernel (ttv_fpt.cuh), one line per slot: 2 x-blocks per CTA, or 1 on thin slabs (below 4 x-blocks two
+            // per CTA leave 148 SMs with too few CTAs); a single x-block keeps the classic kernel
+            if ((zb >= 4 && fp_xb != 1) || fp_xb == 2) {
+                CUtensorMap tmV = make_tmap_xb(vol, N, N, zb, 2, fp_CW, 1);
+                CUtensorMap tmH = make_tmap_xb(vol, N, N, zb, 2, 1, fp_CW);
+                dim3 grid(fp_ndg, fp_ngroups, (zb + 1) / 2);
+                fpt_kernel<EPI, 2><<<grid, FPT_THREADS, fpt_smem, st>>>(tmV, tmH, p, zb, fpt_NS);
+            } else {
+                CUtensorMap tmV = make_tmap_xb(vol, N, N, zb, 1, fp_CW, 1);
+                CUtensorMap tmH = make_tmap_xb(vol, N, N, zb, 1, 1, fp_CW);
+                dim3 grid(fp_ndg, fp_ngroups, zb);
+                fpt_kernel<EPI, 1><<<grid, FPT_THREADS, fpt1_smem, st>>>(tmV, tmH, p, zb, fpt1_NS);
+            }
         } else {
             CUtensorMap tmV = make_tmap(vol, N, N, zb, fp_CW, 1);
             CUtensorMap tmH = make_tmap(vol, N, N, zb, 1, fp_CW);
@@ -680,6 +691,7 @@ public:
     // 2 = table-driven kernel (fpt_kernel / bpt_kernel) whatever the slab thickness
     int fp_variant = 0, bp_variant = 0;
     int bp_xb = 0;                  // x-blocks per CTA of bpt_kernel: 0 = by slab thickness, 2 or 8 (ttv_set_option "bp_xb")
+    int fp_xb = 0;                  // x-blocks per CTA of fpt_kernel: 0 = by slab thickness, 1 or 2 (ttv_set_option "fp_xb")
 
     double read_red(int slot) {
         double v; TTV_CUDA(cudaMemcpyAsync(&v, d_red + slot, sizeof(double), cudaMemcpyDeviceToHost, st)); sync();

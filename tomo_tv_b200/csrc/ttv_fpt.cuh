@@ -29,7 +29,7 @@
 
 namespace ttv {
 
-constexpr int FPT_XB = 2;                       // x-blocks per CTA
+constexpr int FPT_XB = 2;                       // x-blocks per CTA (template parameter XB: 2 by default, 1 on slabs of fewer than 4 x-blocks)
 constexpr int FPT_NW = 16;                      // consumer warps (4 runs each)
 constexpr int FPT_NH = 4;                       // helper warps
 constexpr int FPT_RUNS = FPT_NW * 4;            // 64 runs = 8 angles x 8 detector runs
@@ -39,24 +39,37 @@ constexpr int FPT_MAX_SLOTS = 10;
 static_assert(FPT_RUNS == FP_AG * (FP_DG / FP_RT), "run layout must match the plan of fp_kernel");
 static_assert(FPT_NH * 32 == FPT_RUNS * 2, "one helper thread per half run");
 
-__host__ __device__ inline uint32_t fpt_slot_bytes(int CW) { return (uint32_t)CW * (FPT_XB * 128u) + FPT_TAB; }
+__host__ __device__ inline uint32_t fpt_slot_bytes(int CW, int xb = FPT_XB) { return (uint32_t)CW * ((uint32_t)xb * 128u) + FPT_TAB; }
 
-constexpr uint32_t FPT_CELL = FPT_XB * 128u;    // bytes of one staged cell (2 x-blocks)
+// one predicated LDS.128 (a single x-block per CTA): loaded unless idx == 0xFF
+template <uint32_t CELLB>
+__device__ __forceinline__ void lds_cell1_if(float4& a, uint32_t idx, uint32_t lane_base) {
+    asm volatile(
+        "{\n\t.reg .pred p;\n\t.reg .u32 ad;\n\t"
+        "setp.ne.u32 p, %4, 255;\n\t"
+        "mad.lo.u32 ad, %4, %6, %5;\n\t"
+        "@p ld.shared.v4.f32 {%0,%1,%2,%3}, [ad];\n\t}"
+        : "+f"(a.x), "+f"(a.y), "+f"(a.z), "+f"(a.w)
+        : "r"(idx), "r"(lane_base), "n"(CELLB));
+}
 
-template <int EPI>
+// XB = 2: a lane owns 8 slices (two x-blocks) x 8 detectors.  XB = 1: 4 slices x 8 detectors -- the same kernel for thin slabs
+// (a sharded volume's 64 or 96 slices per GPU), where two x-blocks per CTA would leave 148 SMs with 96 or 192 CTAs.
+template <int EPI, int XB = FPT_XB>
 __global__ void __launch_bounds__(FPT_THREADS, 1)
 fpt_kernel(const __grid_constant__ CUtensorMap tmV, const __grid_constant__ CUtensorMap tmH, const FpParams p, int nxb, int NS)
 {
+    constexpr uint32_t FPT_CELL = XB * 128u;                 // bytes of one staged cell
     extern __shared__ __align__(128) unsigned char smem_raw[];
     const int CW = p.CW, N = p.N;
-    const uint32_t data_bytes = (uint32_t)CW * (FPT_XB * 128u);
+    const uint32_t data_bytes = (uint32_t)CW * (XB * 128u);
     const uint32_t slot_bytes = data_bytes + FPT_TAB;
     uint64_t* full = reinterpret_cast<uint64_t*>(smem_raw + (size_t)NS * slot_bytes);
     uint64_t* empty = full + NS;
 
     const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
     const FpGroup g = p.grp[blockIdx.y];
-    const int dg = blockIdx.x, xb0 = blockIdx.z * FPT_XB;
+    const int dg = blockIdx.x, xb0 = blockIdx.z * XB;
     const uint32_t s_base = smem_u32(smem_raw);
 
     if (tid == 0) {
@@ -169,12 +182,12 @@ fpt_kernel(const __grid_constant__ CUtensorMap tmV, const __grid_constant__ CUte
 #pragma unroll
             for (int t = 0; t < FP_RT; ++t) {
                 const uint32_t e = ent[t];
-                lds_cell_if<FPT_CELL>(E1, E2, entry_iE(e), lb);
-                lds_cell_if<FPT_CELL>(O1, O2, entry_iO(e), lb);
+                if (XB == 2) { lds_cell_if<FPT_CELL>(E1, E2, entry_iE(e), lb); lds_cell_if<FPT_CELL>(O1, O2, entry_iO(e), lb); }
+                else { lds_cell1_if<FPT_CELL>(E1, entry_iE(e), lb); lds_cell1_if<FPT_CELL>(O1, entry_iO(e), lb); }
                 const float wE = entry_wE(e);
                 const float wO = 256.0f - wE;
                 acc1[t].fma(wE, E1); acc1[t].fma(wO, O1);
-                acc2[t].fma(wE, E2); acc2[t].fma(wO, O2);
+                if (XB == 2) { acc2[t].fma(wE, E2); acc2[t].fma(wO, O2); }
             }
         }
         __syncwarp();
@@ -199,7 +212,7 @@ fpt_kernel(const __grid_constant__ CUtensorMap tmV, const __grid_constant__ CUte
                     const float4 a4 = acc1[t].get();
                     fp_emit<EPI>(p, A.orig, d, xb0, lx, make_float4(a4.x * cs, a4.y * cs, a4.z * cs, a4.w * cs), part);
                 }
-                if (xb0 + 1 < nxb) {
+                if (XB == 2 && xb0 + 1 < nxb) {
                     const float4 a4 = acc2[t].get();
                     fp_emit<EPI>(p, A.orig, d, xb0 + 1, lx, make_float4(a4.x * cs, a4.y * cs, a4.z * cs, a4.w * cs), part);
                 }
