@@ -225,3 +225,24 @@ def test_tomofusion_import_paths_resolve_to_this_package(ttv):
     assert tomofusion.determine_gpu_config is ttv.determine_gpu_config
     # the modules are callable like the classes they hold (both spellings are seen in user scripts)
     assert callable(tomoengine) and callable(multigpuengine)
+
+
+def test_digest_goldens_compare_slices_and_norms():
+    """scenarios.digest / compare (fixtures of the 70 x 136^2 geometry hold six slices + whole-array norms): a full result
+    matches its own digest, a change inside a stored slice or anywhere else in the volume is caught, and the ASD-POCS volume
+    tolerance comes from the reference's measured spread."""
+    import scenarios as S
+    rng = np.random.default_rng(0)
+    nx = S.GEOMS["C"][0]
+    full = {"recon": rng.random((nx, 8, 8), dtype=np.float32), "cost": np.float32(3.5)}
+    dg = S.digest("C", full)
+    assert dg["recon"].shape[0] == len(S.DIGEST_SLICES["C"]) and "recon__norm" in dg and dg["cost"] == np.float32(3.5)
+    assert all(r[3] for r in S.compare("fista", full, dg, "C"))
+    bad = {"recon": full["recon"].copy(), "cost": full["cost"]}
+    bad["recon"][S.DIGEST_SLICES["C"][1], 2, 3] += 0.5                  # inside a stored slice
+    assert not all(r[3] for r in S.compare("fista", bad, dg, "C"))
+    bad2 = {"recon": full["recon"].copy(), "cost": full["cost"]}
+    bad2["recon"][5] += 0.5                                              # a slice that is NOT stored: the norm catches it
+    assert not all(r[3] for r in S.compare("fista", bad2, dg, "C"))
+    assert S.digest("A", full) is full                                   # small geometries keep whole arrays
+    assert 1e-3 < S.tol_for("C", "asd", "recon") < 1e-2 and S.tol_for("C", "asd", "dd") == 1e-4 and S.tol_for("C", "fista", "recon") == 1e-4
