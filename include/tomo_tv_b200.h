@@ -212,6 +212,22 @@ int ttv_launch_count(ttv_handle h, long long* n);
 /* algorithmic geometry facts for the roofline: bytes of one volume (V) and one sinogram (S) */
 int ttv_sizes(ttv_handle h, long long* V, long long* S, long long* samples_per_projection);
 
+/* TV value of a DEVICE array without any allocation.  No counterpart in the reference: added
+ * for callers that cannot call cudaMalloc (code under CUDA-graph capture, tight serving loops, harnesses that
+ * forbid it).  Same arithmetic as ttv_tv (tv_3D_kernel, tv_gd.cu:27-47: sum of sqrt(1e-6 + dx^2 + dy^2 + dz^2), periodic
+ * forward differences) on the caller's own layout:
+ *   d_vol   device pointer, float32 [nx][ny][nz], C-contiguous (nx slices of [ny][nz], the layout of ttv_get_recon_all)
+ *   d_tv    device pointer to ONE float32: receives the TV value (stream-ordered; the call does not synchronise)
+ *   stream  a cudaStream_t, or NULL for the default stream; the current device must be the one that owns the pointers
+ * No engine handle, no cudaMalloc / cudaFree or allocating library call: the reduction scratch (one partial sum per 8 rows
+ * + a ticket) is a static __device__ array of TTV_NOALLOC_MAX_ROWS / 8 doubles + 256 bytes (1 MiB + 256 B) that every GPU
+ * loading the library holds until exit.  Limit: nx * ny <= TTV_NOALLOC_MAX_ROWS (e.g. 1024 x 1024 x any nz); larger sizes are
+ * rejected with an error.  All calls share the scratch array: calls that OVERLAP on the GPU (different streams or host
+ * threads) race on it and must be serialised by the caller.  The sum is taken in a fixed order: repeated calls on the same
+ * input give the same bits. */
+#define TTV_NOALLOC_MAX_ROWS 1048576
+int ttv_tv_value_noalloc(const float* d_vol, int nx, int ny, int nz, float* d_tv, void* stream);
+
 #if defined(__GNUC__)
 #pragma GCC visibility pop
 #endif

@@ -431,3 +431,116 @@ int ttv_time_kernel(ttv_handle h, const char* name, int reps, int arg_i, float a
 }  // extern "C"
 
 #include "ttv_capi_fusion.cuh"
+
+#include <mutex>
+// ---------------------------------------------------------------------------------------------------------------------
+// TV value WITHOUT any allocation (ttv_tv_value_noalloc, include/tomo_tv_b200.h).  No counterpart in the reference: added
+// for callers that may not call cudaMalloc (CUDA-graph capture, serving loops).
+//
+// A variant of tv_value_kernel (ttv_tv.cuh:51; arithmetic of tv_3D_kernel, T/gpu/utils/regularizers/tv_gd.cu:27-47) on the
+// caller's own array layout [nx][ny][nz].  The engine's kernel accumulates into a cudaMalloc'ed reduction slot; this one
+// keeps its reduction scratch (one partial sum per CTA + a ticket) in the file-scope array below, which every GPU that
+// loads the library holds until exit: TTV_NOALLOC_MAX_ROWS / 8 doubles + 256 bytes = 1 MiB + 256 B.
+//   * in host code `g_noalloc_scratch` is a host-side stand-in, not a device address: the device address is looked up once
+//     per device with cudaGetSymbolAddress (noalloc_scratch()) and passed to the kernel as an argument;
+//   * all calls share the array and it keeps the last call's contents: the ticket is cleared on the stream before every
+//     launch, the partials are all rewritten before they are read.  Calls that overlap on the GPU (two streams, two host
+//     threads) race on it -- serialise them.
+// The sum is taken in a fixed order (CTA partials in index order), so the result is reproducible bit for bit.
+// ---------------------------------------------------------------------------------------------------------------------
+constexpr long long TTV_NOALLOC_MAX_ROWS_C = TTV_NOALLOC_MAX_ROWS;                 // rows = nx * ny
+constexpr int NOALLOC_MAX_BLOCKS = (int)(TTV_NOALLOC_MAX_ROWS_C / 8);             // 8 rows (warps) per CTA
+constexpr int NOALLOC_TICKET = NOALLOC_MAX_BLOCKS;                                 // element index of the ticket word
+static __device__ __align__(256) double g_noalloc_scratch[NOALLOC_MAX_BLOCKS + 32];
+
+__global__ void __launch_bounds__(256) tv_value_noalloc_kernel(const float* __restrict__ v, int nx, int ny, int nz,
+                                                               double* __restrict__ scratch, float* __restrict__ out)
+{
+    const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
+    const int64_t rows = (int64_t)nx * ny;
+    const int64_t row = (int64_t)blockIdx.x * 8 + w;          // (x, j)
+    double tot = 0.0;
+    if (row < rows) {
+        const int x = (int)(row / ny), j = (int)(row % ny);
+        const float* __restrict__ r0 = v + row * nz;
+        const float* __restrict__ rx = v + ((int64_t)((x + 1) % nx) * ny + j) * nz;
+        const float* __restrict__ rj = v + ((int64_t)x * ny + (j + 1) % ny) * nz;
+        for (int k = lane; k < nz; k += 32) {
+            const float c = r0[k];
+            const float dx = c - rx[k], dy = c - rj[k], dz = c - r0[(k + 1) % nz];
+            tot += (double)sqrtf(1e-6f + dx * dx + dy * dy + dz * dz);
+        }
+    }
+    tot = warp_sum(tot);
+    __shared__ double sh[8];
+    __shared__ unsigned last;
+    if (lane == 0) sh[w] = tot;
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        double s = 0;
+        for (int i = 0; i < 8; ++i) s += sh[i];
+        scratch[blockIdx.x] = s;
+        __threadfence();
+        last = atomicAdd(reinterpret_cast<unsigned*>(scratch + NOALLOC_TICKET), 1u) == gridDim.x - 1 ? 1u : 0u;
+    }
+    __syncthreads();
+    if (!last) return;
+    __threadfence();
+    // last CTA: partials in index order, thread t takes t, t+256, ...
+    double s = 0;
+    for (unsigned i = threadIdx.x; i < gridDim.x; i += 256) s += __ldcg(scratch + i);
+    s = warp_sum(s);
+    __syncthreads();
+    if (lane == 0) sh[w] = s;
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        double t = 0;
+        for (int i = 0; i < 8; ++i) t += sh[i];
+        *out = (float)t;
+    }
+}
+
+// device address of g_noalloc_scratch on the CURRENT device, looked up once per device
+static double* noalloc_scratch() {
+    static std::mutex mu;
+    static double* ptr[64] = {};
+    int dev = -1;
+    TTV_CUDA(cudaGetDevice(&dev));
+    if (dev < 0 || dev >= 64) throw CudaError("ttv_tv_value_noalloc: device ordinal out of range");
+    std::lock_guard<std::mutex> lk(mu);
+    if (!ptr[dev]) {
+        void* p = nullptr;
+        TTV_CUDA(cudaGetSymbolAddress(&p, g_noalloc_scratch));
+        if (!p) throw CudaError("ttv_tv_value_noalloc: cudaGetSymbolAddress returned a null address");
+        ptr[dev] = static_cast<double*>(p);
+    }
+    return ptr[dev];
+}
+
+extern "C" int ttv_tv_value_noalloc(const float* d_vol, int nx, int ny, int nz, float* d_tv, void* stream) {
+    TTV_TRY
+    if (!d_vol || !d_tv) throw CudaError("ttv_tv_value_noalloc: null pointer");
+    if (nx < 1 || ny < 1 || nz < 1) throw CudaError("ttv_tv_value_noalloc: nx, ny, nz must be >= 1");
+    const long long rows = (long long)nx * ny;
+    if (rows > TTV_NOALLOC_MAX_ROWS_C)
+        throw CudaError("ttv_tv_value_noalloc: nx*ny = " + std::to_string(rows) + " exceeds the maximum of " +
+                        std::to_string(TTV_NOALLOC_MAX_ROWS_C) + " rows (TTV_NOALLOC_MAX_ROWS) that the static scratch array holds");
+    int dev = -1;
+    TTV_CUDA(cudaGetDevice(&dev));
+    for (const void* q : {(const void*)d_vol, (const void*)d_tv}) {
+        cudaPointerAttributes at;
+        TTV_CUDA(cudaPointerGetAttributes(&at, q));
+        if (at.type != cudaMemoryTypeDevice && at.type != cudaMemoryTypeManaged)
+            throw CudaError("ttv_tv_value_noalloc: d_vol and d_tv must be device pointers");
+        if (at.type == cudaMemoryTypeDevice && at.device != dev)
+            throw CudaError("ttv_tv_value_noalloc: pointer belongs to device " + std::to_string(at.device) +
+                            ", current device is " + std::to_string(dev));
+    }
+    double* scratch = noalloc_scratch();
+    cudaStream_t st = static_cast<cudaStream_t>(stream);
+    const unsigned blocks = (unsigned)((rows + 7) / 8);
+    TTV_CUDA(cudaMemsetAsync(scratch + NOALLOC_TICKET, 0, sizeof(double), st));     // the ticket must start at zero
+    tv_value_noalloc_kernel<<<blocks, 256, 0, st>>>(d_vol, nx, ny, nz, scratch, d_tv);
+    TTV_LAUNCH_CHECK();
+    TTV_CATCH
+}
