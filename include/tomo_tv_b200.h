@@ -198,7 +198,8 @@ int ttv_timer_stop(ttv_handle h, float* ms);
 /* implementation switches for A/B tests: "fgp_tiled" (1 = TMA-tiled TV-FGP sweep, 0 = first-generation kernel);
  * "fgp_fuse" (1 = two FGP sweeps per launch on a single-volume engine, ttv_fgp2.cuh; 0 = one launch per sweep);
  * "fp_variant" / "bp_variant" (0 = by slab thickness, 1 = classic fp_kernel / bp_kernel, 2 = table-driven fpt_kernel /
- * bpt_kernel); "bp_xb" (x-blocks per CTA of bpt_kernel: 0 = by slab thickness, 2, 8); "sart_cluster" (1 = slice-resident cluster
+ * bpt_kernel); "fp_xb" (x-blocks per CTA of fpt_kernel: 0 = by slab thickness and wave count, 1, 2, 3 = both sizes in one launch,
+ * fptm_kernel, with "fp_mix_n2" leading two-x-block items, -1 = half of them); "bp_xb" (x-blocks per CTA of bpt_kernel: 0 = by slab thickness, 2, 8); "sart_cluster" (1 = slice-resident cluster
  * kernel of ttv_sartc.cuh where at least two slices fit in a cluster's shared memory, 2 = also with one slice per cluster, 0 = one
  * launch pair per angle); "tvgd_march" (1 = register-marching TV-GD gradient kernel, 0 = first-generation kernel).  Every value
  * selects a kernel the GPU tests validate (projector, TV-FGP and TV-GD variants are bit-identical to each other; the two SART

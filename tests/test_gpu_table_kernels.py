@@ -53,7 +53,7 @@ def test_fpt_matches_fp(ttv, nx, n, na):
     vol = rng.random((nx, n, n), dtype=np.float32)
     b = rng.random((nx, na * n), dtype=np.float32) * 3
     outs = []
-    for v, xb in ((1, 0), (2, 2), (2, 1)):           # classic; table-driven with 2 x-blocks per CTA; with 1 (thin slabs)
+    for v, xb in ((1, 0), (2, 2), (2, 1), (2, 3)):   # classic; table-driven with 2 x-blocks per CTA; with 1 (thin slabs); both in one launch
         eng = ttv.tomoengine(nx, n, ang)
         eng.set_option("fp_variant", v); eng.set_option("fp_xb", xb); eng.set_option("bp_variant", 1)
         eng.initialize_initial_volume()

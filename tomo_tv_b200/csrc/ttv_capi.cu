@@ -337,8 +337,9 @@ int ttv_set_option(ttv_handle h, const char* name, int value) {
         if (value < 0 || value > 2) throw CudaError("ttv_set_option: bp_variant must be 0 (by slab thickness), 1 (classic) or 2 (table-driven)");
         e.bp_variant = value;
     }
+    else if (nm == "fp_mix_n2") e.fp_mix_n2 = value;
     else if (nm == "fp_xb") {
-        if (value != 0 && value != 1 && value != 2) throw CudaError("ttv_set_option: fp_xb must be 0 (by slab thickness), 1 or 2");
+        if (value < 0 || value > 3) throw CudaError("ttv_set_option: fp_xb must be 0 (by slab thickness and wave count), 1, 2 or 3 (both CTA sizes in one launch)");
         e.fp_xb = value;
     }
     else if (nm == "bp_xb") {

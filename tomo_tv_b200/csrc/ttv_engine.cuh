@@ -17,6 +17,9 @@
 #include "ttv_elem.cuh"
 #include <vector>
 #include <string>
+#include <map>
+#include <queue>
+#include <functional>
 #include <algorithm>
 #include <random>
 #include <cstring>
@@ -570,7 +573,7 @@ public:
         size_t stage_b = (size_t)TR * CW * 128;
         int S = (int)std::min<size_t>(FP_MAX_STAGES, budget / stage_b);
         if (S < 2) throw CudaError("forward-projector stage does not fit in shared memory");
-        fp_CW = CW; fp_TR = TR; fp_S = S; fp_ngroups = (int)fg.size(); fp_ndg = ndg;
+        fp_CW = CW; fp_TR = TR; fp_S = S; fp_ngroups = (int)fg.size(); fp_ndg = ndg; fp_mix_cache.clear();
         if (CW > 254) throw CudaError("forward-projector window exceeds the table-entry range");
         fpt_NS = (int)std::min<size_t>(FPT_MAX_SLOTS, (size_t)(220 * 1024) / fpt_slot_bytes(CW));
         if (fpt_NS < 3) throw CudaError("forward-projector line slot does not fit in shared memory");
@@ -600,6 +603,7 @@ public:
         TTV_CUDA(cudaFuncSetAttribute(fp_kernel<EPI>, cudaFuncAttributeMaxDynamicSharedMemorySize, optin));
         TTV_CUDA(cudaFuncSetAttribute(fpt_kernel<EPI, 2>, cudaFuncAttributeMaxDynamicSharedMemorySize, optin));
         TTV_CUDA(cudaFuncSetAttribute(fpt_kernel<EPI, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize, optin));
+        TTV_CUDA(cudaFuncSetAttribute(fptm_kernel<EPI>, cudaFuncAttributeMaxDynamicSharedMemorySize, optin));
     }
     template <int EPI> void bp_attr() {
         TTV_CUDA(cudaFuncSetAttribute(bp_kernel<EPI>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)BP_SMEM));
@@ -641,7 +645,15 @@ public:
         if (fp_variant == 2 || (fp_variant == 0 && zb >= 2)) {
             // table-driven kernel (ttv_fpt.cuh), one line per slot: 2 x-blocks per CTA, or 1 on thin slabs (below 4 x-blocks two
             // per CTA leave 148 SMs with too few CTAs); a single x-block keeps the classic kernel
-            if ((zb >= 4 && fp_xb != 1) || fp_xb == 2) {
+            const int n2 = fp_mix_plan(zb);
+            if (n2 >= 0) {
+                // both CTA sizes in one launch (fptm_kernel): n2 pair items, then the other pair items as two CTAs each
+                CUtensorMap tmV2 = make_tmap_xb(vol, N, N, zb, 2, fp_CW, 1), tmH2 = make_tmap_xb(vol, N, N, zb, 2, 1, fp_CW);
+                CUtensorMap tmV1 = make_tmap_xb(vol, N, N, zb, 1, fp_CW, 1), tmH1 = make_tmap_xb(vol, N, N, zb, 1, 1, fp_CW);
+                const int items = fp_ndg * fp_ngroups * ((zb + 1) / 2);
+                fptm_kernel<EPI><<<n2 + 2 * (items - n2), FPT_THREADS, std::max(fpt_smem, fpt1_smem), st>>>(
+                    tmV2, tmH2, tmV1, tmH1, p, zb, fpt_NS, fpt1_NS, fp_ngroups, n2);
+            } else if ((zb >= 4 && fp_xb != 1) || fp_xb == 2) {
                 CUtensorMap tmV = make_tmap_xb(vol, N, N, zb, 2, fp_CW, 1);
                 CUtensorMap tmH = make_tmap_xb(vol, N, N, zb, 2, 1, fp_CW);
                 dim3 grid(fp_ndg, fp_ngroups, (zb + 1) / 2);
@@ -691,7 +703,55 @@ public:
     // 2 = table-driven kernel (fpt_kernel / bpt_kernel) whatever the slab thickness
     int fp_variant = 0, bp_variant = 0;
     int bp_xb = 0;                  // x-blocks per CTA of bpt_kernel: 0 = by slab thickness, 2 or 8 (ttv_set_option "bp_xb")
-    int fp_xb = 0;                  // x-blocks per CTA of fpt_kernel: 0 = by slab thickness, 1 or 2 (ttv_set_option "fp_xb")
+    int fp_xb = 0;                  // x-blocks per CTA of fpt_kernel: 0 = by slab thickness and wave count, 1, 2, or 3 = both sizes
+                                    // in one launch with half of the items each (ttv_set_option "fp_xb")
+    // Number of leading 2-x-block items of a mixed launch (fptm_kernel), or -1 for a launch of one CTA size.  A CTA fills an
+    // SM and the block scheduler hands CTAs out in index order, so the run time of a launch is the makespan of list scheduling
+    // on sm_count machines.  Model fitted to a scan of the split point at 64 ... 512 slices (N = 512, 180 angles,
+    // profiles/r2my_fp_mix_scan.log; 54 points, r.m.s. error 1.4 %): a pair item takes 1, an item of one x-block 0.566 of
+    // that (0.30 against 0.53 ms), CTA times scatter by +-10 % -- which is why a plain launch of many waves is better balanced
+    // than "rounds" suggest (1536 items: the mixed launch gains 0.4 %; 768, 384, 192 items: 3 - 7 %).  The split is taken when
+    // the model promises 2 % over the plain launch.
+    static constexpr double FPT_COST1 = 0.566, FPT_JITTER = 0.10;
+    int fp_mix_n2 = -1;             // with fp_xb == 3: number of leading pair items (ttv_set_option "fp_mix_n2"), -1 = half
+    std::map<int, int> fp_mix_cache;
+    static double fp_makespan(int sms, int n_long, int n_short) {
+        double sum = 0;
+        for (unsigned seed = 1; seed <= 3; ++seed) {
+            std::priority_queue<double, std::vector<double>, std::greater<double>> q;
+            for (int i = 0; i < sms; ++i) q.push(0.0);
+            double end = 0;
+            for (int i = 0; i < n_long + n_short; ++i) {
+                const unsigned h = ((unsigned)i * 2654435761u + seed * 40503u) * 2246822519u;
+                const double u = (double)(h >> 8) / 16777216.0;                     // [0, 1)
+                const double t = q.top() + (i < n_long ? 1.0 : FPT_COST1) * (1.0 - FPT_JITTER + 2.0 * FPT_JITTER * u);
+                q.pop(); q.push(t); end = std::max(end, t);
+            }
+            sum += end;
+        }
+        return sum / 3.0;
+    }
+    int fp_mix_plan(int zb) {
+        if (zb < 2 || fp_xb == 1 || fp_xb == 2) return -1;
+        const int per = fp_ndg * fp_ngroups;
+        const int items = per * ((zb + 1) / 2);      // pair items (the last one of an odd zb holds one x-block)
+        const int pairs = per * (zb / 2);            // items with two x-blocks: only these are worth a long CTA
+        if (fp_xb == 3) return fp_mix_n2 >= 0 ? std::min(fp_mix_n2, items) : items / 2;
+        if (!sm_count) { cudaDeviceProp pr; TTV_CUDA(cudaGetDeviceProperties(&pr, device)); sm_count = pr.multiProcessorCount; }
+        auto it = fp_mix_cache.find(zb);
+        if (it != fp_mix_cache.end()) return it->second;
+        if (items > 12 * sm_count) { fp_mix_cache[zb] = -1; return -1; }      // many waves: the scatter of CTA times balances them
+        const double plain = (zb >= 4) ? fp_makespan(sm_count, items, 0) : fp_makespan(sm_count, 0, per * zb);
+        double best = plain; int best_n2 = -1;
+        const int step = std::max(1, sm_count / 4);
+        for (int n2 = step; n2 <= pairs; n2 += step) {
+            const double t = fp_makespan(sm_count, n2, per * zb - 2 * n2);
+            if (t < best) { best = t; best_n2 = n2; }
+        }
+        if (best > 0.98 * plain) best_n2 = -1;
+        fp_mix_cache[zb] = best_n2;
+        return best_n2;
+    }
 
     double read_red(int slot) {
         double v; TTV_CUDA(cudaMemcpyAsync(&v, d_red + slot, sizeof(double), cudaMemcpyDeviceToHost, st)); sync();

@@ -55,9 +55,10 @@ __device__ __forceinline__ void lds_cell1_if(float4& a, uint32_t idx, uint32_t l
 
 // XB = 2: a lane owns 8 slices (two x-blocks) x 8 detectors.  XB = 1: 4 slices x 8 detectors -- the same kernel for thin slabs
 // (a sharded volume's 64 or 96 slices per GPU), where two x-blocks per CTA would leave 148 SMs with 96 or 192 CTAs.
-template <int EPI, int XB = FPT_XB>
-__global__ void __launch_bounds__(FPT_THREADS, 1)
-fpt_kernel(const __grid_constant__ CUtensorMap tmV, const __grid_constant__ CUtensorMap tmH, const FpParams p, int nxb, int NS)
+// the work of one CTA: detector group `dg` of angle group `gy`, x-blocks xb0 .. xb0 + XB - 1
+template <int EPI, int XB>
+__device__ __forceinline__ void fpt_body(const CUtensorMap& tmV, const CUtensorMap& tmH, const FpParams& p, int nxb, int NS,
+                                         const int dg, const int gy, const int xb0)
 {
     constexpr uint32_t FPT_CELL = XB * 128u;                 // bytes of one staged cell
     extern __shared__ __align__(128) unsigned char smem_raw[];
@@ -68,8 +69,7 @@ fpt_kernel(const __grid_constant__ CUtensorMap tmV, const __grid_constant__ CUte
     uint64_t* empty = full + NS;
 
     const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
-    const FpGroup g = p.grp[blockIdx.y];
-    const int dg = blockIdx.x, xb0 = blockIdx.z * XB;
+    const FpGroup g = p.grp[gy];
     const uint32_t s_base = smem_u32(smem_raw);
 
     if (tid == 0) {
@@ -89,7 +89,7 @@ fpt_kernel(const __grid_constant__ CUtensorMap tmV, const __grid_constant__ CUte
         const CUtensorMap* tm = g.vertical ? &tmV : &tmH;
         const bool producer = (warp == FPT_NW) && (lane == 0);
         if (producer) tma_prefetch_desc(tm);
-        const int* w0tab = p.win0 + ((size_t)blockIdx.y * p.ndg + dg) * (size_t)(((N + p.TR - 1) / p.TR) * p.TR);
+        const int* w0tab = p.win0 + ((size_t)gy * p.ndg + dg) * (size_t)(((N + p.TR - 1) / p.TR) * p.TR);
         // per-angle constants, same operations as fp_kernel / par_fp.cu:63-85,140-161
         const float cth = __cosf(A.theta), sth = __sinf(A.theta);
         float detStep, step;
@@ -222,6 +222,38 @@ fpt_kernel(const __grid_constant__ CUtensorMap tmV, const __grid_constant__ CUte
     if (EPI == FP_KL || EPI == FP_STORE_DIST) {
         double sred = warp_sum((double)part);
         if (lane == 0) atomicAdd(p.red, sred);
+    }
+}
+
+template <int EPI, int XB = FPT_XB>
+__global__ void __launch_bounds__(FPT_THREADS, 1)
+fpt_kernel(const __grid_constant__ CUtensorMap tmV, const __grid_constant__ CUtensorMap tmH, const FpParams p, int nxb, int NS)
+{
+    fpt_body<EPI, XB>(tmV, tmH, p, nxb, NS, blockIdx.x, blockIdx.y, blockIdx.z * XB);
+}
+
+// Both CTA sizes in ONE launch, against wave quantisation.  A CTA fills an SM, so a launch of n work items takes
+// ceil(n / 148) rounds: 1536 items (512 slices x 180 angles x 512 detectors with 2 x-blocks per CTA) are 10.4 waves and
+// run for 11 rounds, the 384 single-x-block items of a 64-slice slab 2.6 waves for 3.  Here the first `n2` items
+// (linear index: detector group fastest, then angle group, then x-block pair) run with 2 x-blocks per CTA and each of the
+// remaining pair items as TWO CTAs of one x-block (0.57 of the time of a pair item): the block scheduler hands out CTAs
+// in index order, so the long CTAs go first and the short ones fill the last round (Engine::fp_mix_plan picks n2).
+// Results do not depend on the split (the two bodies are bit-identical, tests/test_gpu_table_kernels.py).
+template <int EPI>
+__global__ void __launch_bounds__(FPT_THREADS, 1)
+fptm_kernel(const __grid_constant__ CUtensorMap tmV2, const __grid_constant__ CUtensorMap tmH2,
+            const __grid_constant__ CUtensorMap tmV1, const __grid_constant__ CUtensorMap tmH1,
+            const FpParams p, int nxb, int NS2, int NS1, int ngroups, int n2)
+{
+    const int lin = blockIdx.x;
+    const int item = lin < n2 ? lin : n2 + ((lin - n2) >> 1);
+    const int dg = item % p.ndg, gy = (item / p.ndg) % ngroups, z = item / (p.ndg * ngroups);
+    if (lin < n2) {
+        fpt_body<EPI, 2>(tmV2, tmH2, p, nxb, NS2, dg, gy, 2 * z);
+    } else {
+        const int xb0 = 2 * z + ((lin - n2) & 1);
+        if (xb0 >= nxb) return;                               // odd number of x-blocks: the last pair has one
+        fpt_body<EPI, 1>(tmV1, tmH1, p, nxb, NS1, dg, gy, xb0);
     }
 }
 
