@@ -88,3 +88,22 @@ def test_default_choice_by_slab_thickness(ttv):
     assert np.array_equal(recs[1], recs[0])
     with pytest.raises(Exception):
         ttv.tomoengine(nx, n, ang).set_option("bp_variant", 9)
+
+
+@pytest.mark.parametrize("nx", [64, 256])
+def test_fp_planned_mixed_launch_at_slab_sizes(ttv, nx):
+    """The launch plan the engine picks by itself (fp_xb = 0) on the slabs of a 512^3 x 180 volume sharded over 8 and 2 GPUs:
+    384 single-x-block items -> 148 pair CTAs + 88 short ones, 768 pair items -> 740 + 56 short ones (fptm_kernel,
+    Engine::fp_mix_plan).  Same sinogram, bit for bit, as the launch with one CTA size."""
+    n, na = 512, 180
+    rng = np.random.default_rng(nx)
+    ang = np.deg2rad(np.linspace(-90, 90, na, endpoint=False)).astype(np.float32)
+    vol = rng.random((nx, n, n), dtype=np.float32)
+    outs = []
+    for xb in (0, 1):
+        eng = ttv.tomoengine(nx, n, ang)
+        eng.set_option("fp_xb", xb)
+        eng.initialize_initial_volume(); eng.set_recon_all(vol); eng.forward_projection()
+        outs.append(eng.get_model_projections())
+        del eng
+    assert np.array_equal(outs[0], outs[1])
