@@ -90,9 +90,9 @@ def test_default_choice_by_slab_thickness(ttv):
         ttv.tomoengine(nx, n, ang).set_option("bp_variant", 9)
 
 
-@pytest.mark.parametrize("nx", [64, 256])
+@pytest.mark.parametrize("nx", [64, 96, 128, 256])
 def test_fp_planned_mixed_launch_at_slab_sizes(ttv, nx):
-    """The launch plan the engine picks by itself (fp_xb = 0) on the slabs of a 512^3 x 180 volume sharded over 8 and 2 GPUs:
+    """The launch plan the engine picks by itself (fp_xb = 0) on the slabs of a 512^3 x 180 volume sharded over 8, 4 and 2 GPUs (and a three-x-block slab):
     384 single-x-block items -> 148 pair CTAs + 88 short ones, 768 pair items -> 740 + 56 short ones (fptm_kernel,
     Engine::fp_mix_plan).  Same sinogram, bit for bit, as the launch with one CTA size."""
     n, na = 512, 180
