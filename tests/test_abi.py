@@ -50,3 +50,15 @@ def test_no_cpu_fallback(ttv):
         ttv.tomoengine(4, 32, np.zeros(3, np.float32))
     with pytest.raises(SystemExit):
         ttv.pytvlib.check_cuda()
+
+
+def test_noalloc_limit_in_header_matches_python_wrapper():
+    """TTV_NOALLOC_MAX_ROWS (include/tomo_tv_b200.h) is the limit tomo_tv_b200.noalloc documents; the entry point is declared."""
+    import os
+    import re
+    from tomo_tv_b200 import noalloc
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    txt = open(os.path.join(root, "include", "tomo_tv_b200.h")).read()
+    m = re.search(r"#define\s+TTV_NOALLOC_MAX_ROWS\s+(\d+)", txt)
+    assert m and int(m.group(1)) == noalloc.MAX_ROWS
+    assert "int ttv_tv_value_noalloc(const float* d_vol, int nx, int ny, int nz, float* d_tv, void* stream);" in txt
